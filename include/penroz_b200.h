@@ -1,0 +1,149 @@
+/* penroz_b200 — C ABI of the B200 (sm_100a) kernels behind the GPT-2 DDP training step and the KV-cache decode
+ * step of derinworks/penr-oz-neural-network-v3-torch-ddp.
+ *
+ * The reference has no native interface: its hot path is Python calling PyTorch. The entry points below are what a
+ * binding for that path needs — one per PyTorch library call the reference makes on the path (file:line cited per
+ * function, relative to the reference repo). They are called through ctypes from the drop-in Python modules
+ * (neural_net_model / neural_net_layers / ddp / kv_cache) — see INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative PENROZ_ERR_* code; penroz_last_error() gives the text
+ *     (thread-local);
+ *   - all pointers are DEVICE pointers unless stated; the caller owns every buffer, including scratch;
+ *   - no entry point allocates, frees or synchronises unless its comment says so; work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*);
+ *   - dtype codes: 0 = float32, 1 = bfloat16; matrices are row-major with a leading dimension in ELEMENTS;
+ *   - the library is re-entrant (no mutable globals besides a launch counter and per-thread error text).
+ */
+#ifndef PENROZ_B200_H
+#define PENROZ_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PENROZ_OK 0
+#define PENROZ_ERR_ARG (-1)
+#define PENROZ_ERR_CUDA (-2)
+#define PENROZ_ERR_ARCH (-3)
+#define PENROZ_ERR_LIMIT (-4)
+
+#define PENROZ_F32 0
+#define PENROZ_BF16 1
+
+/* GEMM epilogues (penroz_gemm_bf16 / penroz_gemm_f32) */
+#define PENROZ_EPI_STORE 0      /* out = T(acc + bias)                                     */
+#define PENROZ_EPI_GELU 1       /* out = pre = T(acc + bias); out2 = T(gelu(pre))          */
+#define PENROZ_EPI_RESID_F32 2  /* out(f32) = aux(f32) + float(T(acc + bias))              */
+#define PENROZ_EPI_RESID_BF16 3 /* out(bf16) = bf16(float(aux) + float(bf16(acc + bias)))  */
+#define PENROZ_EPI_ACCUM_F32 4  /* out(f32) (+)= acc   (flags bit 1 = accumulate)          */
+#define PENROZ_EPI_DGELU 5      /* out = T(T(acc) * gelu'(aux))                            */
+#define PENROZ_EPI_F32 6        /* out(f32) = acc + bias                                   */
+/* flags: bit0 tanh-GELU (else erf), bit1 accumulate into out, bit2 force 128-wide tile, bit3 force 256-wide tile */
+
+/* ---- library ---- */
+const char* penroz_last_error(void);
+int penroz_abi_version(void);
+/* number of kernel launches this process has issued through the library (for bench.py's gpu_launches) */
+unsigned long long penroz_launch_count(void);
+/* fails with PENROZ_ERR_ARCH unless the current device is compute capability 10.x */
+int penroz_query(int* cc_major, int* cc_minor, int* sm_count);
+
+/* ---- dense contractions: D[M,N] = sum_k A(m,k) B(n,k) ----
+ * Replaces torch nn.Linear forward and its autograd backward (modules built at mappers.py:21,156,158,163,165,172;
+ * run at neural_net_model.py:250-258; backward at neural_net_model.py:650-653).
+ * a_layout/b_layout: 0 = operand stored [rows, K] (K contiguous), 1 = stored [K, rows] (rows contiguous).
+ * penroz_gemm_bf16: tcgen05.mma (TMEM accumulators) fed by TMA; bias is bf16. penroz_gemm_f32: FP32 FMA pipes. */
+int penroz_gemm_bf16(const void* A, long long lda, int a_layout, const void* B, long long ldb, int b_layout, int M,
+                     int N, int K, int epilogue, const void* bias, void* out, long long ldo, void* out2,
+                     long long ldo2, const void* aux, long long ldaux, int flags, void* stream);
+int penroz_gemm_f32(const float* A, long long lda, int a_layout, const float* B, long long ldb, int b_layout, int M,
+                    int N, int K, int epilogue, const float* bias, float* out, long long ldo, float* out2,
+                    long long ldo2, const float* aux, long long ldaux, int flags, void* stream);
+
+/* ---- embedding: out[b,t,:] = wte[idx[b,t]] + wpe[t + pos_offset] ----
+ * Replaces Summation(nn.Embedding, PositionEmbedding) (neural_net_layers.py:98-127) and its backward.
+ * err_flag (device int, may be NULL) is set to 1 when an index is outside [0, V). */
+int penroz_embed_fwd(const long long* idx, const void* wte, const void* wpe, void* out, int B, int T, int C, int V,
+                     int pos_offset, int w_dtype, int out_dtype, int* err_flag, void* stream);
+int penroz_embed_bwd(const long long* idx, const float* dx, float* dwte, float* dwpe, int B, int T, int C, int V,
+                     int pos_offset, void* stream);
+
+/* ---- LayerNorm (eps as given; statistics in fp32) ----
+ * Replaces nn.LayerNorm forward/backward (mappers.py:31,155,162,171). beta may be NULL (bias=False).
+ * Backward also folds in the residual-stream gradient (`add`, neural_net_layers.py:130-135), can emit a bf16 copy
+ * of dx for the next matmul, and accumulates (+=) dgamma, dbeta and — optionally — dcol = column sums of dx
+ * (the bias gradient of the Linear feeding the residual add). Needs caller scratch. */
+int penroz_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* out, float* mean, float* rstd,
+                         int rows, int C, float eps, int x_dtype, int w_dtype, int out_dtype, void* stream);
+size_t penroz_layernorm_bwd_scratch_bytes(int rows, int C);
+int penroz_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                         const void* add, void* dx, void* dx_bf16, float* dgamma, float* dbeta, float* dcol,
+                         int rows, int C, int x_dtype, int w_dtype, int dy_dtype, void* scratch,
+                         size_t scratch_bytes, void* stream);
+
+/* ---- GELU (erf or tanh), standalone forms; the bf16 GEMM fuses both into its epilogues ----
+ * Replaces nn.GELU (mappers.py:25,139,164). */
+int penroz_gelu_fwd(const void* x, void* y, long long n, int tanh_approx, int dtype, void* stream);
+int penroz_gelu_bwd(const void* dy, const void* x, void* dx, long long n, int tanh_approx, int dtype, void* stream);
+
+/* ---- column sums: out[n] (+)= sum_m X[m,n] (bias gradients of nn.Linear) ---- */
+size_t penroz_colsum_scratch_bytes(int M, int N);
+int penroz_colsum(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype, void* scratch,
+                  size_t scratch_bytes, void* stream);
+
+/* ---- dtype cast of a flat buffer (autocast's per-step weight cast, done once per optimizer step here) ---- */
+int penroz_cast(const void* in, void* out, long long n, int in_dtype, int out_dtype, void* stream);
+
+/* ---- causal self-attention on the packed [B,T,3C] QKV buffer (exact fp32 arithmetic path) ----
+ * Replaces CausalSelfAttention.forward, GPT-2 branch (neural_net_layers.py:59-95) and its backward.
+ * out is [B,T,C]; lse is [B,H,T] fp32. D in {32, 64, 128}. */
+int penroz_attn_fwd_simt(const void* qkv, void* out, float* lse, int B, int T, int H, int D, int dtype, void* stream);
+size_t penroz_attn_bwd_scratch_bytes(int B, int T, int H);
+int penroz_attn_bwd_simt(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int B,
+                         int T, int H, int D, int dtype, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- softmax cross-entropy over a chunk of logits rows ----
+ * Replaces F.cross_entropy(logits.view(-1,V), target.view(-1)) (neural_net_model.py:264-267): mean over rows whose
+ * target != ignore_index. ce_rows writes per-row losses and (write_grad) overwrites the logits rows in place with
+ * (softmax - onehot) * grad_scale / n_valid. err_flag is set to 2 for a target outside [0, V). */
+int penroz_ce_count_valid(const long long* targets, int M, long long ignore_index, int* n_valid, void* stream);
+int penroz_ce_rows(void* logits, long long ld, const long long* targets, int M, int V, long long ignore_index,
+                   const int* n_valid, float grad_scale, float* loss_rows, int write_grad, int dtype, int* err_flag,
+                   void* stream);
+int penroz_ce_reduce(const float* loss_rows, int M, const int* n_valid, float out_scale, float* loss_out,
+                     int accumulate, void* stream);
+
+/* ---- AdamW over flat fp32 buffers + global gradient norm ----
+ * Replaces torch.optim.AdamW.step()/zero_grad() (mappers.py:267-274; neural_net_model.py:622,677), same operation
+ * order as torch's single-tensor AdamW. Optionally writes the bf16 shadow weights and zeroes the gradients in the
+ * same pass. grad_mult (device float, may be NULL) scales gradients (clipping; the reference has none). */
+int penroz_adamw_flat(float* p, float* g, float* m, float* v, void* shadow_bf16, long long n, double lr, double beta1,
+                      double beta2, double eps, double weight_decay, long long step, const float* grad_mult,
+                      int zero_grad, void* stream);
+size_t penroz_grad_norm_scratch_bytes(long long n);
+int penroz_grad_norm(const float* g, long long n, float max_norm, float* norm_out, float* mult_out, void* scratch,
+                     size_t scratch_bytes, void* stream);
+
+/* ---- KV-cache decode step ----
+ * Replaces KVCache.append's torch.cat (kv_cache.py:41-68), the cache branch of CausalSelfAttention.forward
+ * (neural_net_layers.py:83-92) and logits[:, -1, :].argmax (neural_net_model.py:393-394).
+ * pool is [n_pages][2][H][PAGE][D]; block_table is int32 [B][max_pages]. */
+int penroz_kv_page_size(void);
+int penroz_kv_append(const void* qkv, void* pool, const int* block_table, int max_pages, int B, int S, int H, int D,
+                     int t0, int dtype, void* stream);
+size_t penroz_attn_decode_scratch_bytes(int B, int H, int D, int t_len);
+int penroz_attn_decode(const void* qkv, const void* pool, const int* block_table, int max_pages, void* out, int B,
+                       int H, int D, int t_len, int dtype, void* scratch, size_t scratch_bytes, void* stream);
+/* few-row Linear (M small): epilogue 0 store, 1 GELU, 2 residual add; out_f32 (optional) receives an fp32 copy */
+int penroz_skinny_linear(const void* x, long long ldx, const void* W, long long ldw, const void* bias, void* out,
+                         long long ldo, const void* aux, long long ldaux, float* out_f32, long long ldo32, int M,
+                         int N, int K, int epilogue, int flags, int dtype, void* stream);
+int penroz_argmax_rows(const void* x, long long ld, int rows, int V, long long* out, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PENROZ_B200_H */

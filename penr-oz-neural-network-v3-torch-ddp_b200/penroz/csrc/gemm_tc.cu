@@ -1,0 +1,484 @@
+// bf16 GEMM on the 5th-gen tensor cores: D[M,N] = sum_k A(m,k) * B(n,k), fp32 accumulate in TMEM.
+//
+// Replaces the cuBLASLt calls torch makes for nn.Linear forward/backward on the reference's
+// hot path (reference: mappers.py:21,156,158,163,165,172 build the nn.Linear modules;
+// neural_net_model.py:250-258 runs them; .backward() at neural_net_model.py:650-653).
+//
+// Design (B200 / sm_100a):
+//   * persistent, warp-specialised CTA (256 threads, one CTA per SM):
+//       warp 0  TMA producer   (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
+//       warp 1  MMA issuer     (one elected lane issues tcgen05.mma cta_group::1 kind::f16, M=128 N=BN K=16)
+//       warp 2  TMEM allocator
+//       warps 4-7 epilogue     (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+//   * smem ring of kStages x {A 128x64, B BNx64} bf16 tiles, full/empty mbarriers
+//   * TMEM double buffered (2 x BN fp32 columns) so the epilogue of tile i overlaps the MMAs of tile i+1
+//   * both operands may be K-major (row-major [rows,K]) or MN-major (row-major [K,rows]); MN-major is what
+//     the weight-gradient (dW = dY^T X) and data-gradient (dX = dY W) contractions need, so no transposed
+//     copies of activations or weights are ever materialised.
+//   * split-K (fp32 red.add epilogue) for the weight-gradient shapes whose output has too few tiles for 148 SMs.
+#include "common.cuh"
+
+namespace penroz {
+
+constexpr int BM = 128;
+constexpr int BK = 64;   // one 128-byte swizzle atom of bf16 along K
+constexpr int UK = 16;   // K per tcgen05.mma for 16-bit inputs
+
+enum Epi {
+    EPI_BF16 = 0,        // out = bf16(acc + bias)
+    EPI_GELU = 1,        // out = pre = bf16(acc + bias); out2 = bf16(gelu(pre))
+    EPI_RESID_F32 = 2,   // out(f32) = aux(f32) + float(bf16(acc + bias))
+    EPI_RESID_BF16 = 3,  // out(bf16) = bf16(float(aux bf16) + float(bf16(acc + bias)))
+    EPI_ACCUM_F32 = 4,   // out(f32) (+)= acc        (beta flag; split-K uses red.add)
+    EPI_DGELU = 5,       // out = bf16(float(bf16(acc)) * gelu'(aux bf16))
+    EPI_F32 = 6,         // out(f32) = acc + bias
+};
+
+struct GemmParams {
+    int M, N, K;
+    int a_mn, b_mn;
+    int tiles_m, tiles_n, splits, kb_per_split, kb_total;
+    const __nv_bfloat16* bias;
+    void* out;
+    long long ldo;
+    void* out2;
+    long long ldo2;
+    const void* aux;
+    long long ldaux;
+    int gelu_tanh;
+    int beta;
+};
+
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_enc, uint32_t sbo_enc) {
+    // cute::UMMA::SmemDescriptor: start[0,14) | LBO[16,30) | SBO[32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)lbo_enc << 16) | ((uint64_t)sbo_enc << 32) |
+           (1ull << 46) | (2ull << 61);
+}
+
+template <int BN> struct GemmCfg {
+    static constexpr int kABytes = BM * BK * 2;
+    static constexpr int kBBytes = BN * BK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = (BN == 256) ? 4 : 6;
+    static constexpr int kTmemCols = 2 * BN;  // 512 or 256: power of two >= 32
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(256, 1)
+gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmParams p) {
+    using Cfg = GemmCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    const uint32_t pad = (1024u - (raw_addr & 1023u)) & 1023u;
+    uint8_t* smem = smem_raw + pad;
+    const uint32_t smem_base = raw_addr + pad;
+    const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+    // barrier slots (8 bytes each): full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], then tmem ptr
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + 2 + s); };
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < Cfg::kStages; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tfull_bar(s), 1);
+            mbar_init(tempty_bar(s), 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(smem_u32(tmem_ptr_smem), Cfg::kTmemCols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int units = p.tiles_m * p.tiles_n * p.splits;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer
+        int s = 0;
+        uint32_t ph = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int tile = u % (p.tiles_m * p.tiles_n);
+            const int split = u / (p.tiles_m * p.tiles_n);
+            const int m0 = (tile / p.tiles_n) * BM;
+            const int n0 = (tile % p.tiles_n) * BN;
+            const int kb0 = split * p.kb_per_split;
+            const int nkb = min(p.kb_per_split, p.kb_total - kb0);
+            for (int kb = 0; kb < nkb; ++kb) {
+                if (lane == 0) {
+                    mbar_wait(empty_bar(s), ph ^ 1u);
+                    mbar_expect_tx(full_bar(s), Cfg::kStageBytes);
+                    const uint32_t sA = smem_base + s * Cfg::kStageBytes;
+                    const uint32_t sB = sA + Cfg::kABytes;
+                    const int k0 = (kb0 + kb) * BK;
+                    if (!p.a_mn) {
+                        tma_load_2d(sA, &tmA, full_bar(s), k0, m0);  // box {64 k, 128 rows}
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j)  // box {64 m, 64 k}
+                            tma_load_2d(sA + j * 8192, &tmA, full_bar(s), m0 + 64 * j, k0);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_2d(sB, &tmB, full_bar(s), k0, n0);  // box {64 k, BN rows}
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(sB + j * 8192, &tmB, full_bar(s), n0 + 64 * j, k0);
+                    }
+                }
+                __syncwarp();
+                if (++s == Cfg::kStages) { s = 0; ph ^= 1u; }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer
+        // cute::UMMA::InstrDescriptor: c_format F32 (1<<4), a/b format BF16 (1<<7, 1<<10),
+        // a_major bit 15, b_major bit 16, N>>3 at [17,23), M>>4 at [24,29)
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
+                               ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+        // K-major SW128: 8-row groups 1024 B apart (SBO), LBO unused (=1). k-step of 16 elems = +32 B.
+        // MN-major SW128: 64-wide MN blocks 8192 B apart (LBO), 8-k groups 1024 B apart (SBO). k-step = 16 rows = +2048 B.
+        const uint32_t a_lbo = p.a_mn ? 512u : 1u, b_lbo = p.b_mn ? 512u : 1u;
+        const uint32_t a_step = p.a_mn ? 2048u : 32u, b_step = p.b_mn ? 2048u : 32u;
+        int s = 0, as = 0;
+        uint32_t ph = 0, aph = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int split = u / (p.tiles_m * p.tiles_n);
+            const int kb0 = split * p.kb_per_split;
+            const int nkb = min(p.kb_per_split, p.kb_total - kb0);
+            if (lane == 0) mbar_wait(tempty_bar(as), aph ^ 1u);
+            __syncwarp();
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+            for (int kb = 0; kb < nkb; ++kb) {
+                if (lane == 0) {
+                    mbar_wait(full_bar(s), ph);
+                    tc_fence_after();
+                    const uint32_t sA = smem_base + s * Cfg::kStageBytes;
+                    const uint32_t sB = sA + Cfg::kABytes;
+#pragma unroll
+                    for (int k4 = 0; k4 < BK / UK; ++k4) {
+                        const uint64_t adesc = make_smem_desc(sA + k4 * a_step, a_lbo, 64u);
+                        const uint64_t bdesc = make_smem_desc(sB + k4 * b_step, b_lbo, 64u);
+                        umma_bf16(d_tmem, adesc, bdesc, idesc, (uint32_t)((kb | k4) != 0));
+                    }
+                    umma_commit(empty_bar(s));               // frees the smem slot once these MMAs retire
+                    if (kb == nkb - 1) umma_commit(tfull_bar(as));  // accumulator ready for the epilogue
+                }
+                __syncwarp();
+                if (++s == Cfg::kStages) { s = 0; ph ^= 1u; }
+            }
+            as ^= 1;
+            if (as == 0) aph ^= 1u;
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------ epilogue (warps 4..7 -> TMEM lane quarters 0..3)
+        const int q = warp - 4;
+        int as = 0;
+        uint32_t aph = 0;
+        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+            const int tile = u % (p.tiles_m * p.tiles_n);
+            const int m0 = (tile / p.tiles_n) * BM;
+            const int n0 = (tile % p.tiles_n) * BN;
+            mbar_wait(tfull_bar(as), aph);
+            tc_fence_after();
+            const int row = m0 + q * 32 + lane;
+            const bool row_ok = row < p.M;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the predicated stores below
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                tmem_ld_wait();
+                const int col0 = n0 + c * 32;
+                if (col0 >= p.N) continue;  // warp-uniform
+                const bool full = (col0 + 32 <= p.N);
+                float acc[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
+                if (EPI != EPI_ACCUM_F32 && EPI != EPI_DGELU && p.bias != nullptr) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (full || col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
+                }
+                if (!row_ok) {
+                    // rows past M (TMA zero-filled): nothing to store
+                } else if (EPI == EPI_BF16 || EPI == EPI_GELU || EPI == EPI_DGELU) {
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * p.ldo + col0;
+                    __nv_bfloat16* o2 = nullptr;
+                    if (EPI == EPI_GELU) o2 = reinterpret_cast<__nv_bfloat16*>(p.out2) + (long long)row * p.ldo2 + col0;
+                    float r[32], r2[32];
+                    if (EPI == EPI_DGELU) {
+                        const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (long long)row * p.ldaux + col0;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            float hv = (full || col0 + i < p.N) ? __bfloat162float(h[i]) : 0.f;
+                            float g = p.gelu_tanh ? gelu_tanh_grad(hv) : gelu_erf_grad(hv);
+                            r[i] = bf16_round(acc[i]) * g;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            r[i] = acc[i];
+                            if (EPI == EPI_GELU) {
+                                float pre = bf16_round(acc[i]);
+                                r2[i] = p.gelu_tanh ? gelu_tanh(pre) : gelu_erf(pre);
+                            }
+                        }
+                    }
+                    if (full && (p.ldo % 8 == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            uint4 w;
+                            w.x = pack_bf16x2(r[8 * j + 0], r[8 * j + 1]);
+                            w.y = pack_bf16x2(r[8 * j + 2], r[8 * j + 3]);
+                            w.z = pack_bf16x2(r[8 * j + 4], r[8 * j + 5]);
+                            w.w = pack_bf16x2(r[8 * j + 6], r[8 * j + 7]);
+                            reinterpret_cast<uint4*>(o)[j] = w;
+                        }
+                    } else {
+                        for (int i = 0; i < 32; ++i)
+                            if (col0 + i < p.N) o[i] = __float2bfloat16_rn(r[i]);
+                    }
+                    if (EPI == EPI_GELU) {
+                        if (full && (p.ldo2 % 8 == 0)) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                uint4 w;
+                                w.x = pack_bf16x2(r2[8 * j + 0], r2[8 * j + 1]);
+                                w.y = pack_bf16x2(r2[8 * j + 2], r2[8 * j + 3]);
+                                w.z = pack_bf16x2(r2[8 * j + 4], r2[8 * j + 5]);
+                                w.w = pack_bf16x2(r2[8 * j + 6], r2[8 * j + 7]);
+                                reinterpret_cast<uint4*>(o2)[j] = w;
+                            }
+                        } else {
+                            for (int i = 0; i < 32; ++i)
+                                if (col0 + i < p.N) o2[i] = __float2bfloat16_rn(r2[i]);
+                        }
+                    }
+                } else if (EPI == EPI_RESID_F32 || EPI == EPI_F32) {
+                    float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
+                    const float* x = (EPI == EPI_RESID_F32)
+                                         ? reinterpret_cast<const float*>(p.aux) + (long long)row * p.ldaux + col0
+                                         : nullptr;
+                    if (full && (p.ldo % 4 == 0) && (EPI == EPI_F32 || p.ldaux % 4 == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (EPI == EPI_RESID_F32) rr = reinterpret_cast<const float4*>(x)[j];
+                            float4 w;
+                            if (EPI == EPI_RESID_F32) {
+                                w.x = rr.x + bf16_round(acc[4 * j + 0]);
+                                w.y = rr.y + bf16_round(acc[4 * j + 1]);
+                                w.z = rr.z + bf16_round(acc[4 * j + 2]);
+                                w.w = rr.w + bf16_round(acc[4 * j + 3]);
+                            } else {
+                                w = make_float4(acc[4 * j + 0], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+                            }
+                            reinterpret_cast<float4*>(o)[j] = w;
+                        }
+                    } else {
+                        for (int i = 0; i < 32; ++i)
+                            if (col0 + i < p.N)
+                                o[i] = (EPI == EPI_RESID_F32) ? x[i] + bf16_round(acc[i]) : acc[i];
+                    }
+                } else if (EPI == EPI_RESID_BF16) {
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * p.ldo + col0;
+                    const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (long long)row * p.ldaux + col0;
+                    for (int i = 0; i < 32; ++i)
+                        if (full || col0 + i < p.N)
+                            o[i] = __float2bfloat16_rn(__bfloat162float(x[i]) + bf16_round(acc[i]));
+                } else {  // EPI_ACCUM_F32
+                    float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
+                    if (p.splits > 1) {
+                        if (full && (p.ldo % 4 == 0)) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + 4 * j),
+                                             "f"(acc[4 * j + 0]), "f"(acc[4 * j + 1]), "f"(acc[4 * j + 2]),
+                                             "f"(acc[4 * j + 3])
+                                             : "memory");
+                        } else {
+                            for (int i = 0; i < 32; ++i)
+                                if (col0 + i < p.N) atomicAdd(o + i, acc[i]);
+                        }
+                    } else if (full && (p.ldo % 4 == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float4 w = make_float4(acc[4 * j + 0], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+                            if (p.beta) {
+                                float4 old = reinterpret_cast<const float4*>(o)[j];
+                                w.x += old.x; w.y += old.y; w.z += old.z; w.w += old.w;
+                            }
+                            reinterpret_cast<float4*>(o)[j] = w;
+                        }
+                    } else {
+                        for (int i = 0; i < 32; ++i)
+                            if (col0 + i < p.N) o[i] = p.beta ? o[i] + acc[i] : acc[i];
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(as));
+            as ^= 1;
+            if (as == 0) aph ^= 1u;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static std::atomic<void*> cached{nullptr};
+    void* fn = cached.load(std::memory_order_acquire);
+    if (fn) return (EncodeTiledFn)fn;
+    cudaDriverEntryPointQueryResult qres;
+    void* sym = nullptr;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !sym) return nullptr;
+    cached.store(sym, std::memory_order_release);
+    return (EncodeTiledFn)sym;
+}
+
+// rows x inner bf16 matrix, row stride ld elements; box {box_inner, box_rows}, 128B swizzle, zero OOB fill
+static int encode_bf16_2d(CUtensorMap* tm, const void* ptr, uint64_t inner, uint64_t rows, uint64_t ld,
+                          uint32_t box_inner, uint32_t box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) { set_error("cuTensorMapEncodeTiled entry point unavailable"); return PENROZ_ERR_CUDA; }
+    cuuint64_t dims[2] = {inner, rows};
+    cuuint64_t strides[1] = {ld * 2};
+    cuuint32_t box[2] = {box_inner, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d): ptr=%p inner=%llu rows=%llu ld=%llu box=%ux%u", (int)r, ptr,
+                  (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)ld, box_inner, box_rows);
+        return PENROZ_ERR_CUDA;
+    }
+    return PENROZ_OK;
+}
+
+template <int BN, int EPI>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
+    using Cfg = GemmCfg<BN>;
+    auto kern = gemm_bf16_tc_kernel<BN, EPI>;
+    static std::atomic<int> configured{0};  // attribute is per-function, per-device; set every time a new device shows up
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!((configured.load() >> dev) & 1)) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+        configured.fetch_or(1 << dev);
+    }
+    kern<<<grid, 256, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
+    count_launch();
+    return check_launch("gemm_bf16_tc");
+}
+
+template <int BN>
+static int dispatch_epi(int epi, const CUtensorMap& a, const CUtensorMap& b, const GemmParams& p, int grid, cudaStream_t st) {
+    switch (epi) {
+        case EPI_BF16: return launch_gemm<BN, EPI_BF16>(a, b, p, grid, st);
+        case EPI_GELU: return launch_gemm<BN, EPI_GELU>(a, b, p, grid, st);
+        case EPI_RESID_F32: return launch_gemm<BN, EPI_RESID_F32>(a, b, p, grid, st);
+        case EPI_RESID_BF16: return launch_gemm<BN, EPI_RESID_BF16>(a, b, p, grid, st);
+        case EPI_ACCUM_F32: return launch_gemm<BN, EPI_ACCUM_F32>(a, b, p, grid, st);
+        case EPI_DGELU: return launch_gemm<BN, EPI_DGELU>(a, b, p, grid, st);
+        case EPI_F32: return launch_gemm<BN, EPI_F32>(a, b, p, grid, st);
+    }
+    set_error("gemm_bf16: unknown epilogue %d", epi);
+    return PENROZ_ERR_ARG;
+}
+
+}  // namespace penroz
+
+using namespace penroz;
+
+extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, const void* B, long long ldb, int b_layout,
+                                int M, int N, int K, int epilogue, const void* bias, void* out, long long ldo,
+                                void* out2, long long ldo2, const void* aux, long long ldaux, int flags,
+                                void* stream) {
+    PENROZ_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
+    PENROZ_REQUIRE(A && B && out, "gemm_bf16: null operand");
+    PENROZ_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_bf16: lda/ldb must be multiples of 8 elements (16 B) for TMA");
+    PENROZ_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0), "gemm_bf16: operands must be 16-byte aligned");
+    PENROZ_REQUIRE(epilogue >= 0 && epilogue <= EPI_F32, "gemm_bf16: bad epilogue %d", epilogue);
+    if (epilogue == EPI_GELU) PENROZ_REQUIRE(out2 != nullptr, "gemm_bf16: GELU epilogue needs out2");
+    if (epilogue == EPI_RESID_F32 || epilogue == EPI_RESID_BF16 || epilogue == EPI_DGELU)
+        PENROZ_REQUIRE(aux != nullptr, "gemm_bf16: epilogue %d needs aux", epilogue);
+    cudaStream_t st = (cudaStream_t)stream;
+
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.a_mn = a_layout ? 1 : 0;
+    p.b_mn = b_layout ? 1 : 0;
+    p.bias = reinterpret_cast<const __nv_bfloat16*>(bias);
+    p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2; p.aux = aux; p.ldaux = ldaux;
+    p.gelu_tanh = (flags & 1) ? 1 : 0;
+    p.beta = (flags & 2) ? 1 : 0;
+
+    const int sms = num_sms();
+    const int tiles_m = (M + BM - 1) / BM;
+    // wide tiles when they still give every SM work; otherwise the 128-wide tile (more CTAs in flight)
+    int bn = 256;
+    if (N <= 128 || (long long)tiles_m * ((N + 255) / 256) < sms) bn = 128;
+    if (flags & 4) bn = 128;
+    if (flags & 8) bn = 256;
+    p.tiles_m = tiles_m;
+    p.tiles_n = (N + bn - 1) / bn;
+    p.kb_total = (K + BK - 1) / BK;
+    p.splits = 1;
+    if (epilogue == EPI_ACCUM_F32) {
+        const int tiles = p.tiles_m * p.tiles_n;
+        if (tiles < sms) p.splits = max(1, min(p.kb_total, sms / tiles));
+        // red.add accumulates into `out`: with beta == 0 the caller must have zeroed it
+        if (p.splits > 1 && !p.beta) {
+            cudaError_t e = cudaMemset2DAsync(out, (size_t)ldo * 4, 0, (size_t)N * 4, (size_t)M, st);
+            if (e != cudaSuccess) { set_error("gemm_bf16: memset: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+        }
+    }
+    p.kb_per_split = (p.kb_total + p.splits - 1) / p.splits;
+    p.splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;  // no empty splits
+
+    CUtensorMap tmA, tmB;
+    int rc;
+    if (!p.a_mn) rc = encode_bf16_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, 64, BM);
+    else         rc = encode_bf16_2d(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, 64);
+    if (rc) return rc;
+    if (!p.b_mn) rc = encode_bf16_2d(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, (uint32_t)bn);
+    else         rc = encode_bf16_2d(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, 64);
+    if (rc) return rc;
+
+    const int units = p.tiles_m * p.tiles_n * p.splits;
+    const int grid = min(units, sms);
+    if (bn == 256) return dispatch_epi<256>(epilogue, tmA, tmB, p, grid, st);
+    return dispatch_epi<128>(epilogue, tmA, tmB, p, grid, st);
+}

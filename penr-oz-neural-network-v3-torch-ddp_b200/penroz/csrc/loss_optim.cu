@@ -1,0 +1,265 @@
+// Softmax cross-entropy over a chunk of LM-head logits (forward + in-place gradient), the fused flat AdamW
+// step, and the global gradient-norm reduction.
+//
+// Reference call sites:
+//   F.cross_entropy(logits.view(-1,V), target.view(-1))   neural_net_model.py:264-267  (mean, ignore_index=-100)
+//   torch.optim.AdamW(...).step()/zero_grad()             mappers.py:267-274, neural_net_model.py:622,677
+// The reference has no gradient clipping (grep: none); the norm/clip path is opt-in (PENROZ_CLIP_GRAD_NORM).
+#include "common.cuh"
+
+namespace penroz {
+
+// ------------------------------------------------------------------ cross entropy
+__global__ void ce_count_valid_kernel(const long long* __restrict__ tgt, int M, long long ignore_index,
+                                      int* __restrict__ n_valid) {
+    __shared__ float red[32];
+    float c = 0.f;
+    for (int i = threadIdx.x; i < M; i += blockDim.x) c += (tgt[i] != ignore_index) ? 1.f : 0.f;
+    c = block_sum(c, red);
+    if (threadIdx.x == 0) *n_valid = (int)(c + 0.5f);
+}
+
+// One CTA per row. Pass 1: online (max, sum-exp) over the row, 16-byte loads. Pass 2 (optional): overwrite the
+// row with d loss / d logits = (softmax - onehot) * grad_scale / n_valid, rounded to the logits dtype (this is
+// what autograd hands the LM-head matmuls under autocast). The second read is served from L2.
+template <typename T>
+__global__ void __launch_bounds__(512)
+ce_rows_kernel(T* __restrict__ logits, long long ld, const long long* __restrict__ tgt, int V,
+               long long ignore_index, const int* __restrict__ n_valid, float grad_scale,
+               float* __restrict__ loss_rows, int write_grad, int* __restrict__ err_flag) {
+    __shared__ float red[32];
+    const int row = blockIdx.x;
+    T* x = logits + (size_t)row * ld;
+    const long long t = tgt[row];
+    const bool ignored = (t == ignore_index);
+    if (!ignored && (t < 0 || t >= V)) {
+        if (threadIdx.x == 0 && err_flag) atomicExch(err_flag, 2);
+    }
+    constexpr int VN = Vec16<T>::N;
+    const bool vec = (ld % VN == 0) && (((uintptr_t)logits) % 16 == 0);
+    const int Vv = vec ? (V / VN) * VN : 0;
+    float m = -INFINITY, s = 0.f;
+    if (!ignored || write_grad) {
+        for (int i = threadIdx.x * VN; i < Vv; i += blockDim.x * VN) {
+            Vec16<T> v;
+            v.load(x + i);
+            float lm = v.get(0);
+#pragma unroll
+            for (int k = 1; k < VN; ++k) lm = fmaxf(lm, v.get(k));
+            const float nm = fmaxf(m, lm);
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k < VN; ++k) acc += __expf(v.get(k) - nm);
+            s = s * __expf(m - nm) + acc;
+            m = nm;
+        }
+        for (int i = Vv + threadIdx.x; i < V; i += blockDim.x) {
+            const float v = to_f32(x[i]);
+            const float nm = fmaxf(m, v);
+            s = s * __expf(m - nm) + __expf(v - nm);
+            m = nm;
+        }
+    }
+    const float gm = block_max(m, red);
+    const float part = (m == -INFINITY) ? 0.f : s * __expf(m - gm);
+    const float gs = block_sum(part, red);
+    const float lse = gm + logf(gs);
+    if (threadIdx.x == 0) {
+        float l = 0.f;
+        if (!ignored && t >= 0 && t < V) l = lse - to_f32(x[t]);
+        loss_rows[row] = l;
+    }
+    if (!write_grad) return;
+    __syncthreads();  // x[t] read above before the row is overwritten
+    const float scale = ignored ? 0.f : grad_scale / (float)max(1, *n_valid);
+    for (int i = threadIdx.x * VN; i < Vv; i += blockDim.x * VN) {
+        Vec16<T> v;
+        v.load(x + i);
+#pragma unroll
+        for (int k = 0; k < VN; ++k) {
+            float p = __expf(v.get(k) - lse);
+            if ((long long)(i + k) == t) p -= 1.f;
+            v.set(k, p * scale);
+        }
+        v.store(x + i);
+    }
+    for (int i = Vv + threadIdx.x; i < V; i += blockDim.x) {
+        float p = __expf(to_f32(x[i]) - lse);
+        if ((long long)i == t) p -= 1.f;
+        x[i] = from_f32<T>(p * scale);
+    }
+}
+
+// loss = sum(loss_rows) / n_valid, single CTA, fixed order (deterministic); *loss_out (+)= loss * out_scale
+__global__ void ce_reduce_kernel(const float* __restrict__ loss_rows, int M, const int* __restrict__ n_valid,
+                                 float out_scale, float* __restrict__ loss_out, int accumulate) {
+    __shared__ float red[32];
+    float s = 0.f;
+    for (int i = threadIdx.x; i < M; i += blockDim.x) s += loss_rows[i];
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) {
+        const int nv = *n_valid;
+        const float l = (nv > 0) ? s / (float)nv : __int_as_float(0x7fc00000);  // torch: mean over zero rows = nan
+        *loss_out = accumulate ? *loss_out + l * out_scale : l * out_scale;
+    }
+}
+
+// ------------------------------------------------------------------ AdamW over flat fp32 buffers
+// Same operation order as torch's _single_tensor_adamw (param decay, lerp, addcmul, sqrt/bias-corr, addcdiv).
+__global__ void adamw_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
+                                  float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, size_t n, float lr_wd_keep,
+                                  float beta1, float beta2, float eps, float step_size_neg, float bc2_sqrt,
+                                  const float* __restrict__ grad_mult, int zero_grad) {
+    const float gm = grad_mult ? *grad_mult : 1.f;
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+    for (; i < n; i += stride) {
+        if (i + 3 < n) {
+            float4 pv = *reinterpret_cast<float4*>(p + i);
+            float4 gv = *reinterpret_cast<float4*>(g + i);
+            float4 mv = *reinterpret_cast<float4*>(m + i);
+            float4 vv = *reinterpret_cast<float4*>(v + i);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float gk = (&gv.x)[k] * gm;
+                float pk = (&pv.x)[k] * lr_wd_keep;
+                float mk = (&mv.x)[k];
+                mk = mk + (gk - mk) * (1.f - beta1);
+                float vk = (&vv.x)[k] * beta2 + ((1.f - beta2) * gk) * gk;
+                const float denom = sqrtf(vk) / bc2_sqrt + eps;
+                pk = pk + step_size_neg * (mk / denom);
+                (&pv.x)[k] = pk; (&mv.x)[k] = mk; (&vv.x)[k] = vk;
+            }
+            *reinterpret_cast<float4*>(p + i) = pv;
+            *reinterpret_cast<float4*>(m + i) = mv;
+            *reinterpret_cast<float4*>(v + i) = vv;
+            if (zero_grad) *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (shadow) {
+                uint2 w;
+                w.x = pack_bf16x2(pv.x, pv.y);
+                w.y = pack_bf16x2(pv.z, pv.w);
+                *reinterpret_cast<uint2*>(shadow + i) = w;
+            }
+        } else {
+            for (size_t k = i; k < n; ++k) {
+                float gk = g[k] * gm;
+                float pk = p[k] * lr_wd_keep;
+                float mk = m[k];
+                mk = mk + (gk - mk) * (1.f - beta1);
+                float vk = v[k] * beta2 + ((1.f - beta2) * gk) * gk;
+                const float denom = sqrtf(vk) / bc2_sqrt + eps;
+                pk = pk + step_size_neg * (mk / denom);
+                p[k] = pk; m[k] = mk; v[k] = vk;
+                if (zero_grad) g[k] = 0.f;
+                if (shadow) shadow[k] = __float2bfloat16_rn(pk);
+            }
+        }
+    }
+}
+
+// sum of squares -> per-block partials (scratch) -> norm, clip multiplier
+__global__ void sumsq_partial_kernel(const float* __restrict__ g, size_t n, float* __restrict__ part) {
+    __shared__ float red[32];
+    float s = 0.f;
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+    for (; i < n; i += stride) {
+        if (i + 3 < n) {
+            float4 v = *reinterpret_cast<const float4*>(g + i);
+            s += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+        } else {
+            for (size_t k = i; k < n; ++k) s += g[k] * g[k];
+        }
+    }
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+__global__ void norm_finish_kernel(const float* __restrict__ part, int nparts, float max_norm,
+                                   float* __restrict__ norm_out, float* __restrict__ mult_out) {
+    __shared__ float red[32];
+    float s = 0.f;
+    for (int i = threadIdx.x; i < nparts; i += blockDim.x) s += part[i];
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) {
+        const float nrm = sqrtf(s);
+        if (norm_out) *norm_out = nrm;
+        if (mult_out) {
+            // torch.nn.utils.clip_grad_norm_: clip_coef = max_norm / (norm + 1e-6), clamped to 1
+            const float c = max_norm / (nrm + 1e-6f);
+            *mult_out = (max_norm > 0.f && c < 1.f) ? c : 1.f;
+        }
+    }
+}
+
+static int flat_grid(size_t n) {
+    size_t g = (n / 4 + 255) / 256;
+    size_t cap = (size_t)num_sms() * 8;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace penroz
+
+using namespace penroz;
+
+extern "C" int penroz_ce_count_valid(const long long* targets, int M, long long ignore_index, int* n_valid,
+                                     void* stream) {
+    PENROZ_REQUIRE(M > 0 && targets && n_valid, "ce_count_valid: bad arguments");
+    ce_count_valid_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(targets, M, ignore_index, n_valid);
+    count_launch();
+    return check_launch("ce_count_valid");
+}
+
+extern "C" int penroz_ce_rows(void* logits, long long ld, const long long* targets, int M, int V,
+                              long long ignore_index, const int* n_valid, float grad_scale, float* loss_rows,
+                              int write_grad, int dtype, int* err_flag, void* stream) {
+    PENROZ_REQUIRE(M > 0 && V > 0 && ld >= V, "ce_rows: bad shape M=%d V=%d ld=%lld", M, V, ld);
+    PENROZ_REQUIRE(logits && targets && loss_rows && n_valid, "ce_rows: null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int threads = V >= 8192 ? 512 : (V >= 1024 ? 256 : 64);
+    if (dtype == BF16)
+        ce_rows_kernel<__nv_bfloat16><<<M, threads, 0, st>>>((__nv_bfloat16*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, write_grad, err_flag);
+    else if (dtype == F32)
+        ce_rows_kernel<float><<<M, threads, 0, st>>>((float*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, write_grad, err_flag);
+    else { set_error("ce_rows: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
+    count_launch();
+    return check_launch("ce_rows");
+}
+
+extern "C" int penroz_ce_reduce(const float* loss_rows, int M, const int* n_valid, float out_scale, float* loss_out,
+                                int accumulate, void* stream) {
+    PENROZ_REQUIRE(M > 0 && loss_rows && n_valid && loss_out, "ce_reduce: bad arguments");
+    ce_reduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(loss_rows, M, n_valid, out_scale, loss_out, accumulate);
+    count_launch();
+    return check_launch("ce_reduce");
+}
+
+extern "C" int penroz_adamw_flat(float* p, float* g, float* m, float* v, void* shadow_bf16, long long n, double lr,
+                                 double beta1, double beta2, double eps, double weight_decay, long long step,
+                                 const float* grad_mult, int zero_grad, void* stream) {
+    PENROZ_REQUIRE(n > 0 && p && g && m && v, "adamw_flat: bad arguments");
+    PENROZ_REQUIRE(step >= 1, "adamw_flat: step must be >= 1");
+    PENROZ_REQUIRE(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0, "adamw_flat: buffers must be 16-byte aligned");
+    const double bc1 = 1.0 - pow(beta1, (double)step);
+    const double bc2 = 1.0 - pow(beta2, (double)step);
+    const double step_size = lr / bc1;
+    const double bc2_sqrt = sqrt(bc2);
+    adamw_flat_kernel<<<flat_grid((size_t)n), 256, 0, (cudaStream_t)stream>>>(
+        p, g, m, v, (__nv_bfloat16*)shadow_bf16, (size_t)n, (float)(1.0 - lr * weight_decay), (float)beta1, (float)beta2,
+        (float)eps, (float)(-step_size), (float)bc2_sqrt, grad_mult, zero_grad);
+    count_launch();
+    return check_launch("adamw_flat");
+}
+
+extern "C" size_t penroz_grad_norm_scratch_bytes(long long n) { return (size_t)flat_grid((size_t)n) * sizeof(float); }
+
+extern "C" int penroz_grad_norm(const float* g, long long n, float max_norm, float* norm_out, float* mult_out,
+                                void* scratch, size_t scratch_bytes, void* stream) {
+    PENROZ_REQUIRE(n > 0 && g, "grad_norm: bad arguments");
+    PENROZ_REQUIRE(scratch && scratch_bytes >= penroz_grad_norm_scratch_bytes(n), "grad_norm: scratch too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = flat_grid((size_t)n);
+    sumsq_partial_kernel<<<grid, 256, 0, st>>>(g, (size_t)n, (float*)scratch);
+    norm_finish_kernel<<<1, 256, 0, st>>>((const float*)scratch, grid, max_norm, norm_out, mult_out);
+    count_launch(2);
+    return check_launch("grad_norm");
+}

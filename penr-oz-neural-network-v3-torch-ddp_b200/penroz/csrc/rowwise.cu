@@ -1,0 +1,512 @@
+// Memory-bound row-wise kernels: embedding gather+add, LayerNorm fwd/bwd (+residual-gradient add, +fused
+// bias-gradient column sums), GELU fwd/bwd, column sums, casts.
+//
+// Reference call sites these replace (all are torch library calls in the reference):
+//   Summation(Embedding, PositionEmbedding)   neural_net_layers.py:98-127
+//   nn.LayerNorm (eps 1e-5)                   mappers.py:31,155,162,171
+//   nn.GELU (erf | tanh)                      mappers.py:25,139,164
+//   ResidualConnection                        neural_net_layers.py:130-135
+// All of them are HBM-bound: one warp per row, 16-byte vector accesses, warp-shuffle reductions.
+#include "common.cuh"
+
+namespace penroz {
+
+// 4 consecutive elements as float4, whatever the storage type
+template <typename T> __device__ __forceinline__ float4 load4(const T* p);
+template <> __device__ __forceinline__ float4 load4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <> __device__ __forceinline__ float4 load4<__nv_bfloat16>(const __nv_bfloat16* p) {
+    uint2 w = *reinterpret_cast<const uint2*>(p);
+    float2 a = unpack_bf16x2(w.x), b = unpack_bf16x2(w.y);
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+template <typename T> __device__ __forceinline__ void store4(T* p, float4 v);
+template <> __device__ __forceinline__ void store4<float>(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+template <> __device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, float4 v) {
+    uint2 w;
+    w.x = pack_bf16x2(v.x, v.y);
+    w.y = pack_bf16x2(v.z, v.w);
+    *reinterpret_cast<uint2*>(p) = w;
+}
+
+// ------------------------------------------------------------------ embedding
+// out[b,t,:] = wte[idx[b,t],:] + wpe[t + pos_offset,:]   (sum formed in fp32, rounded once to TO)
+template <typename TW, typename TO>
+__global__ void embed_fwd_kernel(const long long* __restrict__ idx, const TW* __restrict__ wte,
+                                 const TW* __restrict__ wpe, TO* __restrict__ out, int rows, int T, int C, int V,
+                                 int pos_offset, int* __restrict__ err_flag) {
+    const int warps_per_block = blockDim.x >> 5;
+    const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    long long tok = idx[row];
+    if (tok < 0 || tok >= V) {  // torch raises an index error here; we flag it and clamp
+        if (lane == 0 && err_flag) atomicExch(err_flag, 1);
+        tok = tok < 0 ? 0 : V - 1;
+    }
+    const int t = row % T + pos_offset;
+    const TW* a = wte + (size_t)tok * C;
+    const TW* b = wpe + (size_t)t * C;
+    TO* o = out + (size_t)row * C;
+    if ((C & 3) == 0) {
+        for (int i = lane * 4; i < C; i += 128) {
+            float4 x = load4(a + i), y = load4(b + i);
+            store4(o + i, make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w));
+        }
+    } else {
+        for (int i = lane; i < C; i += 32) o[i] = from_f32<TO>(to_f32(a[i]) + to_f32(b[i]));
+    }
+}
+
+// dwte[idx[b,t],:] += dx[b,t,:] (fp32 red.add: rows collide when a token repeats)
+__global__ void embed_bwd_wte_kernel(const long long* __restrict__ idx, const float* __restrict__ dx,
+                                     float* __restrict__ dwte, int rows, int C, int V) {
+    const int warps_per_block = blockDim.x >> 5;
+    const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    long long tok = idx[row];
+    if (tok < 0 || tok >= V) return;
+    const float* g = dx + (size_t)row * C;
+    float* o = dwte + (size_t)tok * C;
+    for (int i = lane; i < C; i += 32) atomicAdd(o + i, g[i]);
+}
+
+// dwpe[t + off,:] += sum_b dx[b,t,:]  (deterministic: one thread per (t, c4), loop over the batch)
+__global__ void embed_bwd_wpe_kernel(const float* __restrict__ dx, float* __restrict__ dwpe, int B, int T, int C,
+                                     int pos_offset) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T * C) return;
+    const int t = i / C, c = i % C;
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dx[((size_t)b * T + t) * C + c];
+    dwpe[(size_t)(t + pos_offset) * C + c] += s;
+}
+
+// ------------------------------------------------------------------ LayerNorm forward
+// One warp per row. Statistics in fp32 (two-pass: mean, then centred sum of squares), like ATen.
+template <typename TX, typename TW, typename TO>
+__global__ void layernorm_fwd_kernel(const TX* __restrict__ x, const TW* __restrict__ gamma,
+                                     const TW* __restrict__ beta, TO* __restrict__ out, float* __restrict__ mean_out,
+                                     float* __restrict__ rstd_out, int rows, int C, float eps) {
+    const int warps_per_block = blockDim.x >> 5;
+    const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const TX* xr = x + (size_t)row * C;
+    TO* o = out + (size_t)row * C;
+    const bool vec = (C & 3) == 0;
+    float s = 0.f;
+    if (vec) {
+        for (int i = lane * 4; i < C; i += 128) { float4 v = load4(xr + i); s += (v.x + v.y) + (v.z + v.w); }
+    } else {
+        for (int i = lane; i < C; i += 32) s += to_f32(xr[i]);
+    }
+    const float mean = warp_sum(s) / (float)C;
+    float q = 0.f;
+    if (vec) {
+        for (int i = lane * 4; i < C; i += 128) {
+            float4 v = load4(xr + i);
+            float a = v.x - mean, b = v.y - mean, c = v.z - mean, d = v.w - mean;
+            q += (a * a + b * b) + (c * c + d * d);
+        }
+    } else {
+        for (int i = lane; i < C; i += 32) { float a = to_f32(xr[i]) - mean; q += a * a; }
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)C + eps);
+    if (lane == 0) {
+        if (mean_out) mean_out[row] = mean;
+        if (rstd_out) rstd_out[row] = rstd;
+    }
+    if (vec) {
+        for (int i = lane * 4; i < C; i += 128) {
+            float4 v = load4(xr + i), g = load4(gamma + i);
+            float4 b = beta ? load4(beta + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            store4(o + i, make_float4((v.x - mean) * rstd * g.x + b.x, (v.y - mean) * rstd * g.y + b.y,
+                                      (v.z - mean) * rstd * g.z + b.z, (v.w - mean) * rstd * g.w + b.w));
+        }
+    } else {
+        for (int i = lane; i < C; i += 32)
+            o[i] = from_f32<TO>((to_f32(xr[i]) - mean) * rstd * to_f32(gamma[i]) + (beta ? to_f32(beta[i]) : 0.f));
+    }
+}
+
+// ------------------------------------------------------------------ LayerNorm backward
+// dx_total = add + rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)); written as TX and (optionally) a bf16 copy.
+// Column reductions (dgamma = sum dy*xhat, dbeta = sum dy, dcol = sum bf16-or-f32(dx_total)) are accumulated in
+// registers by each warp over its rows, combined across the block in shared memory and written to
+// scratch[block][3][C]; layernorm_bwd_reduce_kernel then folds the per-block partials into the gradients.
+// J = ceil(C / 128): float4 chunks per lane.
+template <typename TX, typename TW, typename TG, int J, bool DCOL>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, const TW* __restrict__ gamma,
+                     const float* __restrict__ mean, const float* __restrict__ rstd, const TX* __restrict__ add,
+                     TX* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ scratch, int rows,
+                     int C) {
+    extern __shared__ float sred[];  // [8 warps][C]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float4 ag[J], ab[J], ac[DCOL ? J : 1];
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        ag[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        ab[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (DCOL) ac[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float4 gam[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int i = (lane + 32 * j) * 4;
+        gam[j] = (i < C) ? load4(gamma + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
+        const TG* dyr = dy + (size_t)row * C;
+        const TX* xr = x + (size_t)row * C;
+        const float mu = mean[row], rs = rstd[row];
+        float4 dyv[J], xh[J];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            const int i = (lane + 32 * j) * 4;
+            if (i < C) {
+                dyv[j] = load4(dyr + i);
+                float4 xv = load4(xr + i);
+                xh[j] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+                const float4 g = gam[j];
+                const float a = dyv[j].x * g.x, b = dyv[j].y * g.y, c = dyv[j].z * g.z, d = dyv[j].w * g.w;
+                s1 += (a + b) + (c + d);
+                s2 += (a * xh[j].x + b * xh[j].y) + (c * xh[j].z + d * xh[j].w);
+                ag[j].x += dyv[j].x * xh[j].x; ag[j].y += dyv[j].y * xh[j].y;
+                ag[j].z += dyv[j].z * xh[j].z; ag[j].w += dyv[j].w * xh[j].w;
+                ab[j].x += dyv[j].x; ab[j].y += dyv[j].y; ab[j].z += dyv[j].z; ab[j].w += dyv[j].w;
+            }
+        }
+        s1 = warp_sum(s1) / (float)C;
+        s2 = warp_sum(s2) / (float)C;
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            const int i = (lane + 32 * j) * 4;
+            if (i < C) {
+                const float4 g = gam[j];
+                float4 r;
+                r.x = rs * (dyv[j].x * g.x - s1 - xh[j].x * s2);
+                r.y = rs * (dyv[j].y * g.y - s1 - xh[j].y * s2);
+                r.z = rs * (dyv[j].z * g.z - s1 - xh[j].z * s2);
+                r.w = rs * (dyv[j].w * g.w - s1 - xh[j].w * s2);
+                if (add) {
+                    float4 a = load4(add + (size_t)row * C + i);
+                    r.x += a.x; r.y += a.y; r.z += a.z; r.w += a.w;
+                }
+                store4(dx + (size_t)row * C + i, r);
+                if (dx_bf16) store4(dx_bf16 + (size_t)row * C + i, r);
+                if (DCOL) {
+                    // the bias gradient of the Linear that produced this residual branch sums the gradient
+                    // as that Linear sees it: rounded to bf16 when a bf16 copy is requested
+                    if (dx_bf16) { r.x = bf16_round(r.x); r.y = bf16_round(r.y); r.z = bf16_round(r.z); r.w = bf16_round(r.w); }
+                    ac[j].x += r.x; ac[j].y += r.y; ac[j].z += r.z; ac[j].w += r.w;
+                }
+            }
+        }
+    }
+    // block combine: quantity by quantity through sred[8][C]
+    const int nq = DCOL ? 3 : 2;
+    for (int qn = 0; qn < nq; ++qn) {
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+            const int i = (lane + 32 * j) * 4;
+            if (i < C) {
+                const float4 v = (qn == 0) ? ag[j] : (qn == 1) ? ab[j] : ac[DCOL ? j : 0];
+                *reinterpret_cast<float4*>(sred + (size_t)warp * C + i) = v;
+            }
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < C; c += blockDim.x) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s += sred[(size_t)w * C + c];
+            scratch[((size_t)blockIdx.x * 3 + qn) * C + c] = s;
+        }
+    }
+}
+
+// out_q[c] += sum_blocks scratch[b][q][c]   (fixed order: deterministic)
+__global__ void layernorm_bwd_reduce_kernel(const float* __restrict__ scratch, int nblocks, int C,
+                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                            float* __restrict__ dcol) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const int qn = blockIdx.y;
+    float* dst = (qn == 0) ? dgamma : (qn == 1) ? dbeta : dcol;
+    if (!dst) return;
+    float s = 0.f;
+    for (int b = 0; b < nblocks; ++b) s += scratch[((size_t)b * 3 + qn) * C + c];
+    dst[c] += s;
+}
+
+// ------------------------------------------------------------------ GELU
+template <typename T>
+__global__ void gelu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, size_t n, int tanh_approx) {
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+    for (; i + 3 < n; i += stride) {
+        float4 v = load4(x + i);
+        if (tanh_approx) v = make_float4(gelu_tanh(v.x), gelu_tanh(v.y), gelu_tanh(v.z), gelu_tanh(v.w));
+        else v = make_float4(gelu_erf(v.x), gelu_erf(v.y), gelu_erf(v.z), gelu_erf(v.w));
+        store4(y + i, v);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        for (size_t k = n & ~(size_t)3; k < n; ++k) {
+            float v = to_f32(x[k]);
+            y[k] = from_f32<T>(tanh_approx ? gelu_tanh(v) : gelu_erf(v));
+        }
+}
+template <typename T>
+__global__ void gelu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, size_t n,
+                                int tanh_approx) {
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+    for (; i + 3 < n; i += stride) {
+        float4 v = load4(x + i), g = load4(dy + i);
+        if (tanh_approx) v = make_float4(gelu_tanh_grad(v.x), gelu_tanh_grad(v.y), gelu_tanh_grad(v.z), gelu_tanh_grad(v.w));
+        else v = make_float4(gelu_erf_grad(v.x), gelu_erf_grad(v.y), gelu_erf_grad(v.z), gelu_erf_grad(v.w));
+        store4(dx + i, make_float4(g.x * v.x, g.y * v.y, g.z * v.z, g.w * v.w));
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        for (size_t k = n & ~(size_t)3; k < n; ++k) {
+            float v = to_f32(x[k]);
+            dx[k] = from_f32<T>(to_f32(dy[k]) * (tanh_approx ? gelu_tanh_grad(v) : gelu_erf_grad(v)));
+        }
+}
+
+// ------------------------------------------------------------------ column sums (bias gradients)
+// part[y][n] = sum over this block's row slice of X[m,n]; 32 x 8 threads, 4 columns per thread.
+template <typename T>
+__global__ void colsum_partial_kernel(const T* __restrict__ X, long long ld, int M, int N, float* __restrict__ part) {
+    __shared__ float4 sm[8][32];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int col = (blockIdx.x * 32 + tx) * 4;
+    const int rows_per = (M + gridDim.y - 1) / gridDim.y;
+    const int r0 = blockIdx.y * rows_per, r1 = min(M, r0 + rows_per);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (col + 3 < N) {
+        for (int r = r0 + ty; r < r1; r += 8) {
+            float4 v = load4(X + (size_t)r * ld + col);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+    } else if (col < N) {
+        for (int r = r0 + ty; r < r1; r += 8)
+            for (int k = 0; k < 4 && col + k < N; ++k) (&s.x)[k] += to_f32(X[(size_t)r * ld + col + k]);
+    }
+    sm[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && col < N) {
+        for (int k = 1; k < 8; ++k) { float4 v = sm[k][tx]; s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+        for (int k = 0; k < 4 && col + k < N; ++k) part[(size_t)blockIdx.y * N + col + k] = (&s.x)[k];
+    }
+}
+__global__ void colsum_reduce_kernel(const float* __restrict__ part, int nparts, int N, float* __restrict__ out,
+                                     int accumulate) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= N) return;
+    float s = 0.f;
+    for (int p = 0; p < nparts; ++p) s += part[(size_t)p * N + c];
+    out[c] = accumulate ? out[c] + s : s;
+}
+
+template <typename TI, typename TO>
+__global__ void cast_kernel(const TI* __restrict__ in, TO* __restrict__ out, size_t n) {
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+    for (; i + 3 < n; i += stride) store4(out + i, load4(in + i));
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        for (size_t k = n & ~(size_t)3; k < n; ++k) out[k] = from_f32<TO>(to_f32(in[k]));
+}
+
+template <int J, bool DCOL, typename TX, typename TW, typename TG>
+static void launch_ln_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                          const void* add, void* dx, void* dx_bf16, float* scratch, int rows, int C, int grid,
+                          cudaStream_t st) {
+    auto k = layernorm_bwd_kernel<TX, TW, TG, J, DCOL>;
+    const size_t smem = (size_t)8 * C * sizeof(float);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k<<<grid, 256, smem, st>>>((const TG*)dy, (const TX*)x, (const TW*)gamma, mean, rstd, (const TX*)add, (TX*)dx,
+                              (__nv_bfloat16*)dx_bf16, scratch, rows, C);
+}
+
+template <bool DCOL, typename TX, typename TW, typename TG>
+static int dispatch_ln_bwd_j(int J, const void* dy, const void* x, const void* gamma, const float* mean,
+                             const float* rstd, const void* add, void* dx, void* dx_bf16, float* scratch, int rows,
+                             int C, int grid, cudaStream_t st) {
+#define PENROZ_LN_CASE(j) \
+    if (J <= j) { launch_ln_bwd<j, DCOL, TX, TW, TG>(dy, x, gamma, mean, rstd, add, dx, dx_bf16, scratch, rows, C, grid, st); return 0; }
+    PENROZ_LN_CASE(1) PENROZ_LN_CASE(2) PENROZ_LN_CASE(4) PENROZ_LN_CASE(6) PENROZ_LN_CASE(8)
+    if (!DCOL) { PENROZ_LN_CASE(13) PENROZ_LN_CASE(16) }
+#undef PENROZ_LN_CASE
+    return -1;
+}
+
+}  // namespace penroz
+
+using namespace penroz;
+
+static inline int grid_for(size_t n_vec4, int threads) {
+    size_t g = (n_vec4 + threads - 1) / threads;
+    size_t cap = (size_t)num_sms() * 16;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+extern "C" int penroz_embed_fwd(const long long* idx, const void* wte, const void* wpe, void* out, int B, int T,
+                                int C, int V, int pos_offset, int w_dtype, int out_dtype, int* err_flag,
+                                void* stream) {
+    PENROZ_REQUIRE(B > 0 && T > 0 && C > 0 && V > 0, "embed_fwd: bad shape");
+    PENROZ_REQUIRE(pos_offset >= 0, "embed_fwd: negative position offset");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int rows = B * T, wpb = 8;
+    const int grid = (rows + wpb - 1) / wpb;
+    if (w_dtype == F32 && out_dtype == F32)
+        embed_fwd_kernel<float, float><<<grid, wpb * 32, 0, st>>>(idx, (const float*)wte, (const float*)wpe, (float*)out, rows, T, C, V, pos_offset, err_flag);
+    else if (w_dtype == BF16 && out_dtype == BF16)
+        embed_fwd_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, wpb * 32, 0, st>>>(idx, (const __nv_bfloat16*)wte, (const __nv_bfloat16*)wpe, (__nv_bfloat16*)out, rows, T, C, V, pos_offset, err_flag);
+    else { set_error("embed_fwd: unsupported dtype combination w=%d out=%d", w_dtype, out_dtype); return PENROZ_ERR_ARG; }
+    count_launch();
+    return check_launch("embed_fwd");
+}
+
+extern "C" int penroz_embed_bwd(const long long* idx, const float* dx, float* dwte, float* dwpe, int B, int T, int C,
+                                int V, int pos_offset, void* stream) {
+    PENROZ_REQUIRE(B > 0 && T > 0 && C > 0 && V > 0, "embed_bwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int rows = B * T;
+    embed_bwd_wte_kernel<<<(rows + 7) / 8, 256, 0, st>>>(idx, dx, dwte, rows, C, V);
+    embed_bwd_wpe_kernel<<<(T * C + 255) / 256, 256, 0, st>>>(dx, dwpe, B, T, C, pos_offset);
+    count_launch(2);
+    return check_launch("embed_bwd");
+}
+
+extern "C" int penroz_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* out, float* mean,
+                                    float* rstd, int rows, int C, float eps, int x_dtype, int w_dtype, int out_dtype,
+                                    void* stream) {
+    PENROZ_REQUIRE(rows > 0 && C > 0, "layernorm_fwd: bad shape rows=%d C=%d", rows, C);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = (rows + 7) / 8;
+#define LN_FWD(TX, TW, TO) layernorm_fwd_kernel<TX, TW, TO><<<grid, 256, 0, st>>>((const TX*)x, (const TW*)gamma, (const TW*)beta, (TO*)out, mean, rstd, rows, C, eps)
+    if (x_dtype == F32 && w_dtype == F32 && out_dtype == BF16) LN_FWD(float, float, __nv_bfloat16);
+    else if (x_dtype == F32 && w_dtype == F32 && out_dtype == F32) LN_FWD(float, float, float);
+    else if (x_dtype == BF16 && w_dtype == BF16 && out_dtype == BF16) LN_FWD(__nv_bfloat16, __nv_bfloat16, __nv_bfloat16);
+    else { set_error("layernorm_fwd: unsupported dtypes x=%d w=%d out=%d", x_dtype, w_dtype, out_dtype); return PENROZ_ERR_ARG; }
+#undef LN_FWD
+    count_launch();
+    return check_launch("layernorm_fwd");
+}
+
+// scratch must hold penroz_layernorm_bwd_scratch_bytes(rows, C) bytes
+static int ln_bwd_grid(int rows) {
+    int g = (rows + 7) / 8;
+    int cap = 2 * num_sms();
+    return g < cap ? g : cap;
+}
+extern "C" size_t penroz_layernorm_bwd_scratch_bytes(int rows, int C) {
+    return (size_t)ln_bwd_grid(rows) * 3 * (size_t)C * sizeof(float);
+}
+
+namespace penroz {
+int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                       const void* add, void* dx, void* dx_bf16, float* dgamma, float* dbeta, float* dcol,
+                       int rows, int C, int x_dtype, int w_dtype, int dy_dtype, float* scratch, cudaStream_t st) {
+    PENROZ_REQUIRE(rows > 0 && C > 0, "layernorm_bwd: bad shape rows=%d C=%d", rows, C);
+    PENROZ_REQUIRE((C & 3) == 0, "layernorm_bwd: C=%d must be a multiple of 4", C);
+    PENROZ_REQUIRE(C <= 2048, "layernorm_bwd: C=%d exceeds the supported 2048", C);
+    PENROZ_REQUIRE(scratch != nullptr, "layernorm_bwd: scratch is required");
+    const int J = (C + 127) / 128;
+    const int grid = ln_bwd_grid(rows);
+    const bool fuse_dcol = dcol != nullptr && J <= 8;
+    int rc = -1;
+#define LN_BWD(TX, TW, TG)                                                                                              \
+    rc = fuse_dcol ? dispatch_ln_bwd_j<true, TX, TW, TG>(J, dy, x, gamma, mean, rstd, add, dx, dx_bf16, scratch, rows, C, grid, st) \
+                   : dispatch_ln_bwd_j<false, TX, TW, TG>(J, dy, x, gamma, mean, rstd, add, dx, dx_bf16, scratch, rows, C, grid, st)
+    if (x_dtype == F32 && w_dtype == F32 && dy_dtype == BF16) { LN_BWD(float, float, __nv_bfloat16); }
+    else if (x_dtype == F32 && w_dtype == F32 && dy_dtype == F32) { LN_BWD(float, float, float); }
+    else { set_error("layernorm_bwd: unsupported dtypes x=%d w=%d dy=%d", x_dtype, w_dtype, dy_dtype); return PENROZ_ERR_ARG; }
+#undef LN_BWD
+    if (rc != 0) { set_error("layernorm_bwd: no kernel for C=%d", C); return PENROZ_ERR_ARG; }
+    dim3 rg((C + 255) / 256, fuse_dcol ? 3 : 2);
+    layernorm_bwd_reduce_kernel<<<rg, 256, 0, st>>>(scratch, grid, C, dgamma, dbeta, fuse_dcol ? dcol : nullptr);
+    count_launch(2);
+    int e = check_launch("layernorm_bwd");
+    if (e) return e;
+    if (dcol != nullptr && !fuse_dcol) {
+        // wide rows: column sums of the written gradient as a separate pass (re-uses the same scratch)
+        const void* src = dx_bf16 ? dx_bf16 : dx;
+        const int parts = 32;
+        dim3 g((C + 127) / 128, parts);
+        if (dx_bf16) colsum_partial_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)src, C, rows, C, scratch);
+        else colsum_partial_kernel<float><<<g, 256, 0, st>>>((const float*)src, C, rows, C, scratch);
+        colsum_reduce_kernel<<<(C + 255) / 256, 256, 0, st>>>(scratch, parts, C, dcol, 1);
+        count_launch(2);
+        return check_launch("layernorm_bwd/colsum");
+    }
+    return PENROZ_OK;
+}
+}  // namespace penroz
+
+extern "C" int penroz_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                                    const float* rstd, const void* add, void* dx, void* dx_bf16, float* dgamma,
+                                    float* dbeta, float* dcol, int rows, int C, int x_dtype, int w_dtype,
+                                    int dy_dtype, void* scratch, size_t scratch_bytes, void* stream) {
+    PENROZ_REQUIRE(scratch_bytes >= penroz_layernorm_bwd_scratch_bytes(rows, C),
+                   "layernorm_bwd: scratch too small (%zu < %zu)", scratch_bytes, penroz_layernorm_bwd_scratch_bytes(rows, C));
+    return layernorm_bwd_impl(dy, x, gamma, mean, rstd, add, dx, dx_bf16, dgamma, dbeta, dcol, rows, C, x_dtype,
+                              w_dtype, dy_dtype, (float*)scratch, (cudaStream_t)stream);
+}
+
+extern "C" int penroz_gelu_fwd(const void* x, void* y, long long n, int tanh_approx, int dtype, void* stream) {
+    PENROZ_REQUIRE(n > 0, "gelu_fwd: empty");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = grid_for((size_t)(n + 3) / 4, 256);
+    if (dtype == F32) gelu_fwd_kernel<float><<<grid, 256, 0, st>>>((const float*)x, (float*)y, (size_t)n, tanh_approx);
+    else if (dtype == BF16) gelu_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, (size_t)n, tanh_approx);
+    else { set_error("gelu_fwd: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
+    count_launch();
+    return check_launch("gelu_fwd");
+}
+
+extern "C" int penroz_gelu_bwd(const void* dy, const void* x, void* dx, long long n, int tanh_approx, int dtype,
+                               void* stream) {
+    PENROZ_REQUIRE(n > 0, "gelu_bwd: empty");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = grid_for((size_t)(n + 3) / 4, 256);
+    if (dtype == F32) gelu_bwd_kernel<float><<<grid, 256, 0, st>>>((const float*)dy, (const float*)x, (float*)dx, (size_t)n, tanh_approx);
+    else if (dtype == BF16) gelu_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, (size_t)n, tanh_approx);
+    else { set_error("gelu_bwd: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
+    count_launch();
+    return check_launch("gelu_bwd");
+}
+
+extern "C" size_t penroz_colsum_scratch_bytes(int M, int N) { (void)M; return (size_t)32 * (size_t)N * sizeof(float); }
+
+// out[n] (+)= sum_m X[m,n]   (bias gradient of a Linear whose output gradient is X)
+extern "C" int penroz_colsum(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype,
+                             void* scratch, size_t scratch_bytes, void* stream) {
+    PENROZ_REQUIRE(M > 0 && N > 0, "colsum: bad shape");
+    PENROZ_REQUIRE(scratch && scratch_bytes >= penroz_colsum_scratch_bytes(M, N), "colsum: scratch too small");
+    PENROZ_REQUIRE(ld % 4 == 0, "colsum: ld must be a multiple of 4");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int parts = 32;
+    dim3 g((N + 127) / 128, parts);
+    if (dtype == F32) colsum_partial_kernel<float><<<g, 256, 0, st>>>((const float*)X, ld, M, N, (float*)scratch);
+    else if (dtype == BF16) colsum_partial_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)X, ld, M, N, (float*)scratch);
+    else { set_error("colsum: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
+    colsum_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>((const float*)scratch, parts, N, out, accumulate);
+    count_launch(2);
+    return check_launch("colsum");
+}
+
+extern "C" int penroz_cast(const void* in, void* out, long long n, int in_dtype, int out_dtype, void* stream) {
+    PENROZ_REQUIRE(n > 0, "cast: empty");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = grid_for((size_t)(n + 3) / 4, 256);
+    if (in_dtype == F32 && out_dtype == BF16) cast_kernel<float, __nv_bfloat16><<<grid, 256, 0, st>>>((const float*)in, (__nv_bfloat16*)out, (size_t)n);
+    else if (in_dtype == BF16 && out_dtype == F32) cast_kernel<__nv_bfloat16, float><<<grid, 256, 0, st>>>((const __nv_bfloat16*)in, (float*)out, (size_t)n);
+    else { set_error("cast: unsupported %d -> %d", in_dtype, out_dtype); return PENROZ_ERR_ARG; }
+    count_launch();
+    return check_launch("cast");
+}

@@ -1,0 +1,223 @@
+"""Torch-tensor front ends of the C-ABI entry points (include/penroz_b200.h).
+
+torch is only the allocator and stream owner here: every function takes CUDA tensors, passes raw device pointers
+and the current stream through ctypes, and returns tensors it allocated. No function falls back to a torch op.
+"""
+import math
+
+import torch
+
+from . import _lib
+from ._lib import (BF16, EPI_ACCUM_F32, EPI_DGELU, EPI_F32, EPI_GELU, EPI_RESID_BF16, EPI_RESID_F32, EPI_STORE, F32,
+                   FLAG_ACCUM, FLAG_TANH, dt, lib, ptr, stream)
+
+
+def _chk(t: torch.Tensor, name: str):
+    if not t.is_cuda:
+        raise _lib.PenrozError(f"{name} must be a CUDA tensor (penroz_b200 has no CPU path)")
+    if not t.is_contiguous() and t.dim() != 2:
+        raise _lib.PenrozError(f"{name} must be contiguous")
+
+
+def _mat(t: torch.Tensor, name: str):
+    """2-D view with unit inner stride -> (tensor, ld)."""
+    _chk(t, name)
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise _lib.PenrozError(f"{name} must be a row-major 2-D tensor, got shape {tuple(t.shape)} strides {t.stride()}")
+    return t, t.stride(0)
+
+
+def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=None, out2=None, aux=None,
+         tanh=False, accumulate=False, out_dtype=None, flags_extra=0):
+    """D[M,N] = sum_k A(m,k) B(n,k) with a fused epilogue. a: [M,K] (layout 0) or [K,M] (layout 1); b likewise.
+
+    bf16 operands -> tcgen05 kernel; fp32 operands -> FP32-pipe kernel. Returns out (and out2 for the GELU epilogue).
+    """
+    a, lda = _mat(a, "a")
+    b, ldb = _mat(b, "b")
+    M, K = (a.shape[0], a.shape[1]) if a_layout == 0 else (a.shape[1], a.shape[0])
+    N, Kb = (b.shape[0], b.shape[1]) if b_layout == 0 else (b.shape[1], b.shape[0])
+    if K != Kb:
+        raise _lib.PenrozError(f"gemm: K mismatch {K} vs {Kb}")
+    if a.dtype != b.dtype:
+        raise _lib.PenrozError(f"gemm: operand dtypes differ ({a.dtype} vs {b.dtype})")
+    is_bf16 = a.dtype == torch.bfloat16
+    if out is None:
+        if out_dtype is None:
+            out_dtype = torch.float32 if (epilogue in (EPI_RESID_F32, EPI_ACCUM_F32, EPI_F32) or not is_bf16) else torch.bfloat16
+        out = torch.empty((M, N), device=a.device, dtype=out_dtype)
+    if epilogue == EPI_GELU and out2 is None:
+        out2 = torch.empty((M, N), device=a.device, dtype=out.dtype)
+    flags = (FLAG_TANH if tanh else 0) | (FLAG_ACCUM if accumulate else 0) | flags_extra
+    ldo = out.stride(0)
+    ldo2 = out2.stride(0) if out2 is not None else 0
+    ldaux = aux.stride(0) if aux is not None else 0
+    if is_bf16:
+        lib().gemm_bf16(ptr(a), lda, a_layout, ptr(b), ldb, b_layout, M, N, K, epilogue, ptr(bias), ptr(out), ldo,
+                        ptr(out2), ldo2, ptr(aux), ldaux, flags, stream())
+    else:
+        epi = EPI_STORE if epilogue == EPI_F32 else epilogue
+        lib().gemm_f32(ptr(a), lda, a_layout, ptr(b), ldb, b_layout, M, N, K, epi, ptr(bias), ptr(out), ldo,
+                       ptr(out2), ldo2, ptr(aux), ldaux, flags, stream())
+    return (out, out2) if epilogue == EPI_GELU else out
+
+
+def embed_fwd(idx, wte, wpe, pos_offset=0, out_dtype=None, err_flag=None):
+    B, T = idx.shape
+    V, C = wte.shape
+    out_dtype = out_dtype or wte.dtype
+    out = torch.empty((B, T, C), device=idx.device, dtype=out_dtype)
+    lib().embed_fwd(ptr(idx), ptr(wte), ptr(wpe), ptr(out), B, T, C, V, pos_offset, dt(wte),
+                    F32 if out_dtype == torch.float32 else BF16, ptr(err_flag), stream())
+    return out
+
+
+def embed_bwd(idx, dx, dwte, dwpe, pos_offset=0):
+    B, T = idx.shape
+    V, C = dwte.shape
+    lib().embed_bwd(ptr(idx), ptr(dx), ptr(dwte), ptr(dwpe), B, T, C, V, pos_offset, stream())
+
+
+def layernorm_fwd(x, gamma, beta, eps=1e-5, out_dtype=None, save_stats=True):
+    C = x.shape[-1]
+    rows = x.numel() // C
+    out_dtype = out_dtype or x.dtype
+    out = torch.empty(x.shape, device=x.device, dtype=out_dtype)
+    mean = torch.empty(rows, device=x.device, dtype=torch.float32) if save_stats else None
+    rstd = torch.empty(rows, device=x.device, dtype=torch.float32) if save_stats else None
+    lib().layernorm_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(out), ptr(mean), ptr(rstd), rows, C, eps, dt(x), dt(gamma),
+                        F32 if out_dtype == torch.float32 else BF16, stream())
+    return out, mean, rstd
+
+
+def layernorm_bwd_scratch(rows, C, device):
+    n = lib().layernorm_bwd_scratch_bytes(rows, C)
+    return torch.empty(n, device=device, dtype=torch.uint8)
+
+
+def layernorm_bwd(dy, x, gamma, mean, rstd, *, add=None, dgamma=None, dbeta=None, dcol=None, want_bf16=False,
+                  scratch=None):
+    """Returns (dx, dx_bf16|None); accumulates (+=) into dgamma/dbeta/dcol."""
+    C = x.shape[-1]
+    rows = x.numel() // C
+    dx = torch.empty_like(x)
+    dxb = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16) if want_bf16 else None
+    if scratch is None:
+        scratch = layernorm_bwd_scratch(rows, C, x.device)
+    lib().layernorm_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(mean), ptr(rstd), ptr(add), ptr(dx), ptr(dxb), ptr(dgamma),
+                        ptr(dbeta), ptr(dcol), rows, C, dt(x), dt(gamma), dt(dy), ptr(scratch), scratch.numel(),
+                        stream())
+    return dx, dxb
+
+
+def gelu_fwd(x, tanh=False):
+    y = torch.empty_like(x)
+    lib().gelu_fwd(ptr(x), ptr(y), x.numel(), int(tanh), dt(x), stream())
+    return y
+
+
+def gelu_bwd(dy, x, tanh=False):
+    dx = torch.empty_like(x)
+    lib().gelu_bwd(ptr(dy), ptr(x), ptr(dx), x.numel(), int(tanh), dt(x), stream())
+    return dx
+
+
+def colsum(x2d, out, accumulate=True, scratch=None):
+    x2d, ld = _mat(x2d, "x")
+    M, N = x2d.shape
+    if scratch is None:
+        scratch = torch.empty(lib().colsum_scratch_bytes(M, N), device=x2d.device, dtype=torch.uint8)
+    lib().colsum(ptr(x2d), ld, M, N, ptr(out), int(accumulate), dt(x2d), ptr(scratch), scratch.numel(), stream())
+    return out
+
+
+def cast(src, dst):
+    lib().cast(ptr(src), ptr(dst), src.numel(), dt(src), dt(dst), stream())
+    return dst
+
+
+def attn_fwd(qkv, H, want_lse=True):
+    """qkv [B,T,3C] -> (out [B,T,C], lse [B,H,T])."""
+    B, T, C3 = qkv.shape
+    C = C3 // 3
+    D = C // H
+    out = torch.empty((B, T, C), device=qkv.device, dtype=qkv.dtype)
+    lse = torch.empty((B, H, T), device=qkv.device, dtype=torch.float32) if want_lse else None
+    lib().attn_fwd_simt(ptr(qkv), ptr(out), ptr(lse), B, T, H, D, dt(qkv), stream())
+    return out, lse
+
+
+def attn_bwd(qkv, out, dout, lse, H, scratch=None):
+    B, T, C3 = qkv.shape
+    D = (C3 // 3) // H
+    dqkv = torch.empty_like(qkv)
+    if scratch is None:
+        scratch = torch.empty(lib().attn_bwd_scratch_bytes(B, T, H), device=qkv.device, dtype=torch.uint8)
+    lib().attn_bwd_simt(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, dt(qkv), ptr(scratch),
+                        scratch.numel(), stream())
+    return dqkv
+
+
+def ce_count_valid(targets, n_valid, ignore_index=-100):
+    lib().ce_count_valid(ptr(targets), targets.numel(), ignore_index, ptr(n_valid), stream())
+
+
+def ce_rows(logits2d, targets, n_valid, loss_rows, *, V=None, grad_scale=1.0, write_grad=True, ignore_index=-100,
+            err_flag=None):
+    logits2d, ld = _mat(logits2d, "logits")
+    M = logits2d.shape[0]
+    V = V if V is not None else logits2d.shape[1]
+    lib().ce_rows(ptr(logits2d), ld, ptr(targets), M, V, ignore_index, ptr(n_valid), float(grad_scale),
+                  ptr(loss_rows), int(write_grad), dt(logits2d), ptr(err_flag), stream())
+
+
+def ce_reduce(loss_rows, n_valid, loss_out, out_scale=1.0, accumulate=False):
+    lib().ce_reduce(ptr(loss_rows), loss_rows.numel(), ptr(n_valid), float(out_scale), ptr(loss_out), int(accumulate),
+                    stream())
+
+
+def adamw_flat(p, g, m, v, shadow, *, lr, betas, eps, weight_decay, step, grad_mult=None, zero_grad=False):
+    lib().adamw_flat(ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), p.numel(), float(lr), float(betas[0]),
+                     float(betas[1]), float(eps), float(weight_decay), int(step), ptr(grad_mult), int(zero_grad),
+                     stream())
+
+
+def grad_norm(g, max_norm, norm_out, mult_out, scratch=None):
+    if scratch is None:
+        scratch = torch.empty(lib().grad_norm_scratch_bytes(g.numel()), device=g.device, dtype=torch.uint8)
+    lib().grad_norm(ptr(g), g.numel(), float(max_norm), ptr(norm_out), ptr(mult_out), ptr(scratch), scratch.numel(),
+                    stream())
+
+
+def kv_append(qkv2d, pool, block_table, B, S, H, D, t0):
+    lib().kv_append(ptr(qkv2d), ptr(pool), ptr(block_table), block_table.shape[1], B, S, H, D, t0, dt(qkv2d), stream())
+
+
+def attn_decode(qkv2d, pool, block_table, B, H, D, t_len, scratch=None):
+    out = torch.empty((B, H * D), device=qkv2d.device, dtype=qkv2d.dtype)
+    if scratch is None:
+        scratch = torch.empty(lib().attn_decode_scratch_bytes(B, H, D, t_len), device=qkv2d.device, dtype=torch.uint8)
+    lib().attn_decode(ptr(qkv2d), ptr(pool), ptr(block_table), block_table.shape[1], ptr(out), B, H, D, t_len,
+                      dt(qkv2d), ptr(scratch), scratch.numel(), stream())
+    return out
+
+
+def skinny_linear(x, W, bias=None, *, epilogue=0, aux=None, tanh=False, out=None, out_f32=None):
+    x, ldx = _mat(x, "x")
+    W, ldw = _mat(W, "W")
+    M, K = x.shape
+    N = W.shape[0]
+    if out is None and out_f32 is None:
+        out = torch.empty((M, N), device=x.device, dtype=x.dtype)
+    lib().skinny_linear(ptr(x), ldx, ptr(W), ldw, ptr(bias), ptr(out), out.stride(0) if out is not None else 0,
+                        ptr(aux), aux.stride(0) if aux is not None else 0, ptr(out_f32),
+                        out_f32.stride(0) if out_f32 is not None else 0, M, N, K, epilogue, int(tanh), dt(x), stream())
+    return out if out is not None else out_f32
+
+
+def argmax_rows(x2d, V=None):
+    x2d, ld = _mat(x2d, "x")
+    rows = x2d.shape[0]
+    out = torch.empty(rows, device=x2d.device, dtype=torch.int64)
+    lib().argmax_rows(ptr(x2d), ld, rows, V if V is not None else x2d.shape[1], ptr(out), dt(x2d), stream())
+    return out

@@ -1,0 +1,328 @@
+"""Per-kernel parity on the GPU: every C-ABI entry point against a plain PyTorch fp32 statement of the same op.
+
+Tolerances are written beside each check. bf16 kernels are compared with an fp32 reference evaluated on the same
+bf16-rounded inputs; the bound is a few bf16 ulps of the output scale (2^-8 relative) unless stated.
+"""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from penroz import _lib
+    _lib.require_device()
+    return torch.device("cuda:0")
+
+
+def rel_err(a, b):
+    a = a.float()
+    b = b.float()
+    return ((a - b).abs().max() / (b.abs().max() + 1e-12)).item()
+
+
+# ------------------------------------------------------------------ GEMM (tcgen05)
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 768), (300, 200, 136), (1024, 2304, 768),
+                                    (77, 50257, 768), (4096, 768, 3072)])
+@pytest.mark.parametrize("al,bl", [(0, 0), (0, 1), (1, 1), (1, 0)])
+def test_gemm_bf16_layouts(dev, M, N, K, al, bl):
+    from penroz import ops
+    if N == 50257 and bl == 1:
+        pytest.skip("MN-major operand needs ld % 8 == 0")
+    if al == 1 and M % 8:
+        pytest.skip("MN-major operand needs ld % 8 == 0")
+    torch.manual_seed(M + N + K)
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = torch.randn(N, K, device=dev).bfloat16()
+    ref = A.float() @ B.float().t()
+    a_in = A if al == 0 else A.t().contiguous()
+    b_in = B if bl == 0 else B.t().contiguous()
+    out = ops.gemm(a_in, b_in, a_layout=al, b_layout=bl, epilogue=ops.EPI_F32)
+    torch.cuda.synchronize()
+    # fp32 accumulation of exact bf16 products: only summation-order noise
+    assert rel_err(out, ref) < 2e-5, f"fp32-out rel err {rel_err(out, ref)}"
+    out_b = ops.gemm(a_in, b_in, a_layout=al, b_layout=bl, epilogue=ops.EPI_STORE)
+    assert torch.equal(out_b, out.bfloat16()) or rel_err(out_b, ref) < 4e-3
+
+
+@pytest.mark.parametrize("bn_flag", [4, 8])
+def test_gemm_bf16_epilogues(dev, bn_flag):
+    from penroz import ops
+    torch.manual_seed(0)
+    M, N, K = 512, 768, 256
+    A = torch.randn(M, K, device=dev).bfloat16()
+    W = (torch.randn(N, K, device=dev) * 0.05).bfloat16()
+    bias = torch.randn(N, device=dev).bfloat16()
+    acc = A.float() @ W.float().t() + bias.float()
+    pre_ref = acc.bfloat16()
+    out = ops.gemm(A, W, epilogue=ops.EPI_STORE, bias=bias, flags_extra=bn_flag)
+    assert rel_err(out, acc) < 4e-3
+    for tanh in (False, True):
+        pre, post = ops.gemm(A, W, epilogue=ops.EPI_GELU, bias=bias, tanh=tanh, flags_extra=bn_flag)
+        g_ref = F.gelu(pre.float(), approximate="tanh" if tanh else "none")
+        assert rel_err(pre, acc) < 4e-3
+        assert rel_err(post, g_ref) < 4e-3
+        # DGELU: out = bf16(acc) * gelu'(h)
+        h = pre
+        hh = h.float().requires_grad_(True)
+        F.gelu(hh, approximate="tanh" if tanh else "none").sum().backward()
+        d = ops.gemm(A, W, epilogue=ops.EPI_DGELU, aux=h, tanh=tanh, flags_extra=bn_flag)
+        d_ref = (A.float() @ W.float().t()).bfloat16().float() * hh.grad
+        assert rel_err(d, d_ref) < 6e-3
+    resid = torch.randn(M, N, device=dev)
+    o = ops.gemm(A, W, epilogue=ops.EPI_RESID_F32, bias=bias, aux=resid, flags_extra=bn_flag)
+    assert (o - (resid + pre_ref.float())).abs().max().item() < 0.05
+    assert rel_err(o, resid + acc) < 4e-3
+    rb = resid.bfloat16()
+    ob = ops.gemm(A, W, epilogue=ops.EPI_RESID_BF16, bias=bias, aux=rb, flags_extra=bn_flag)
+    assert rel_err(ob, rb.float() + acc) < 8e-3
+    # accumulate (weight-gradient form, split-K engaged: few tiles, long K)
+    dY = torch.randn(4096, 256, device=dev).bfloat16()
+    X = torch.randn(4096, 384, device=dev).bfloat16()
+    ref = dY.float().t() @ X.float()
+    g0 = torch.zeros(256, 384, device=dev)
+    ops.gemm(dY, X, a_layout=1, b_layout=1, epilogue=ops.EPI_ACCUM_F32, out=g0, flags_extra=bn_flag)
+    assert rel_err(g0, ref) < 2e-5
+    ops.gemm(dY, X, a_layout=1, b_layout=1, epilogue=ops.EPI_ACCUM_F32, out=g0, accumulate=True, flags_extra=bn_flag)
+    assert rel_err(g0, 2 * ref) < 2e-5
+
+
+def test_gemm_f32(dev):
+    from penroz import ops
+    torch.manual_seed(1)
+    for (M, N, K, al, bl) in [(100, 70, 33, 0, 0), (256, 128, 64, 1, 0), (65, 193, 128, 0, 1), (128, 65, 128, 1, 1)]:
+        A = torch.randn(M, K, device=dev)
+        B = torch.randn(N, K, device=dev)
+        bias = torch.randn(N, device=dev)
+        ref = (A.double() @ B.double().t() + bias.double()).float()
+        a_in = A if al == 0 else A.t().contiguous()
+        b_in = B if bl == 0 else B.t().contiguous()
+        out = ops.gemm(a_in, b_in, a_layout=al, b_layout=bl, bias=bias)
+        assert rel_err(out, ref) < 1e-5
+    A = torch.randn(64, 128, device=dev); W = torch.randn(96, 128, device=dev) * 0.1; b = torch.randn(96, device=dev)
+    pre, post = ops.gemm(A, W, epilogue=ops.EPI_GELU, bias=b)
+    assert rel_err(post, F.gelu(A @ W.t() + b)) < 1e-5
+    r = torch.randn(64, 96, device=dev)
+    o = ops.gemm(A, W, epilogue=ops.EPI_RESID_F32, bias=b, aux=r)
+    assert rel_err(o, r + A @ W.t() + b) < 1e-5
+
+
+# ------------------------------------------------------------------ row-wise kernels
+@pytest.mark.parametrize("C", [128, 768, 1024, 1600])
+def test_layernorm_fwd_bwd(dev, C):
+    from penroz import ops
+    torch.manual_seed(C)
+    rows = 1000
+    x = torch.randn(rows, C, device=dev) * 2 + 0.5
+    g = torch.randn(C, device=dev)
+    b = torch.randn(C, device=dev)
+    ref = F.layer_norm(x, (C,), g, b, 1e-5)
+    out, mean, rstd = ops.layernorm_fwd(x, g, b, out_dtype=torch.float32)
+    assert rel_err(out, ref) < 1e-5   # fp32 in/out: summation order only
+    outb, _, _ = ops.layernorm_fwd(x, g, b, out_dtype=torch.bfloat16)
+    assert rel_err(outb, ref) < 4e-3  # one bf16 rounding of the output
+    out_nb, _, _ = ops.layernorm_fwd(x, g, None, out_dtype=torch.float32)
+    assert rel_err(out_nb, F.layer_norm(x, (C,), g, None, 1e-5)) < 1e-5
+    # backward, fp32 dy, with residual add and fused column sums
+    xr = x.clone().requires_grad_(True); gr = g.clone().requires_grad_(True); br = b.clone().requires_grad_(True)
+    dy = torch.randn(rows, C, device=dev)
+    add = torch.randn(rows, C, device=dev)
+    F.layer_norm(xr, (C,), gr, br, 1e-5).backward(dy)
+    dgam = torch.zeros(C, device=dev); dbet = torch.zeros(C, device=dev); dcol = torch.zeros(C, device=dev)
+    dx, dxb = ops.layernorm_bwd(dy, x, g, mean, rstd, add=add, dgamma=dgam, dbeta=dbet, dcol=dcol, want_bf16=False)
+    assert rel_err(dx, xr.grad + add) < 2e-5
+    assert rel_err(dgam, gr.grad) < 2e-5
+    assert rel_err(dbet, br.grad) < 2e-5
+    assert rel_err(dcol, (xr.grad + add).sum(0)) < 1e-4
+    # bf16 dy (autocast), bf16 copy of dx, accumulate semantics (+=)
+    dyb = dy.bfloat16()
+    xr.grad = None; gr.grad = None; br.grad = None
+    F.layer_norm(xr, (C,), gr, br, 1e-5).backward(dyb.float())
+    dx2, dxb2 = ops.layernorm_bwd(dyb, x, g, mean, rstd, add=None, dgamma=dgam, dbeta=dbet, dcol=None, want_bf16=True)
+    assert rel_err(dx2, xr.grad) < 2e-5
+    assert torch.equal(dxb2, dx2.bfloat16())
+    assert rel_err(dgam, gr.grad * 2) < 1e-2  # second accumulation used the bf16-rounded dy
+
+
+def test_embedding(dev):
+    from penroz import ops
+    torch.manual_seed(3)
+    V, T, C, B = 65, 64, 128, 16
+    wte = torch.randn(V, C, device=dev); wpe = torch.randn(T, C, device=dev)
+    idx = torch.randint(0, V, (B, T), device=dev)
+    out = ops.embed_fwd(idx, wte, wpe)
+    assert torch.equal(out, wte[idx] + wpe[None, :, :])
+    out5 = ops.embed_fwd(idx[:, :7], wte, wpe, pos_offset=5)
+    assert torch.equal(out5, wte[idx[:, :7]] + wpe[None, 5:12, :])
+    ob = ops.embed_fwd(idx, wte.bfloat16(), wpe.bfloat16())
+    assert torch.equal(ob, (wte.bfloat16()[idx] + wpe.bfloat16()[None]))
+    dx = torch.randn(B, T, C, device=dev)
+    dwte = torch.zeros_like(wte); dwpe = torch.zeros_like(wpe)
+    ops.embed_bwd(idx, dx, dwte, dwpe)
+    ref_wte = torch.zeros_like(wte).index_add_(0, idx.view(-1), dx.view(-1, C))
+    assert rel_err(dwte, ref_wte) < 1e-5  # atomics: order noise only
+    assert rel_err(dwpe, dx.sum(0)) < 1e-6
+    flag = torch.zeros(1, device=dev, dtype=torch.int32)
+    bad = idx.clone(); bad[0, 0] = V + 3
+    ops.embed_fwd(bad, wte, wpe, err_flag=flag)
+    assert flag.item() == 1
+
+
+@pytest.mark.parametrize("tanh", [False, True])
+def test_gelu_and_colsum_and_cast(dev, tanh):
+    from penroz import ops
+    torch.manual_seed(4)
+    x = torch.randn(1000, 515, device=dev) * 3
+    appr = "tanh" if tanh else "none"
+    assert rel_err(ops.gelu_fwd(x, tanh), F.gelu(x, approximate=appr)) < 2e-6
+    xr = x.clone().requires_grad_(True)
+    dy = torch.randn_like(x)
+    F.gelu(xr, approximate=appr).backward(dy)
+    assert rel_err(ops.gelu_bwd(dy, x, tanh), xr.grad) < 5e-6
+    xb = x.bfloat16()
+    assert rel_err(ops.gelu_fwd(xb, tanh), F.gelu(xb.float(), approximate=appr)) < 4e-3
+    y = torch.randn(4099, 772, device=dev)
+    out = torch.ones(772, device=dev)
+    ops.colsum(y, out, accumulate=True)
+    assert rel_err(out, 1 + y.sum(0)) < 1e-5
+    outb = torch.zeros(772, device=dev)
+    ops.colsum(y.bfloat16(), outb, accumulate=False)
+    assert rel_err(outb, y.bfloat16().float().sum(0)) < 1e-5
+    dst = torch.empty(x.numel(), device=dev, dtype=torch.bfloat16)
+    ops.cast(x.view(-1), dst)
+    assert torch.equal(dst, x.view(-1).bfloat16())
+
+
+# ------------------------------------------------------------------ attention (exact path)
+@pytest.mark.parametrize("B,T,H,D,dtype", [(2, 64, 4, 32, torch.float32), (2, 200, 3, 64, torch.float32),
+                                            (1, 1024, 2, 64, torch.bfloat16), (2, 96, 2, 128, torch.float32)])
+def test_attention_simt(dev, B, T, H, D, dtype):
+    from penroz import ops
+    torch.manual_seed(T)
+    C = H * D
+    qkv = (torch.randn(B, T, 3 * C, device=dev)).to(dtype)
+    q, k, v = [t.view(B, T, H, D).transpose(1, 2).float().requires_grad_(True) for t in qkv.split(C, dim=2)]
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    out, lse = ops.attn_fwd(qkv, H)
+    ref_out = ref.transpose(1, 2).reshape(B, T, C)
+    tol = 1e-5 if dtype == torch.float32 else 8e-3
+    assert rel_err(out, ref_out) < tol
+    s = (q @ k.transpose(-1, -2)) / math.sqrt(D)
+    mask = torch.ones(T, T, device=dev, dtype=torch.bool).tril()
+    lse_ref = torch.logsumexp(s.masked_fill(~mask, float("-inf")), dim=-1)
+    assert rel_err(lse, lse_ref) < 1e-5
+    dout = torch.randn(B, T, C, device=dev).to(dtype)
+    ref.backward(dout.float().view(B, T, H, D).transpose(1, 2))
+    dqkv = ops.attn_bwd(qkv, out, dout, lse, H)
+    ref_d = torch.cat([t.grad.transpose(1, 2).reshape(B, T, C) for t in (q, k, v)], dim=2)
+    btol = 2e-5 if dtype == torch.float32 else 1.5e-2
+    assert rel_err(dqkv, ref_d) < btol
+
+
+# ------------------------------------------------------------------ cross entropy, AdamW, grad norm
+@pytest.mark.parametrize("V,ld,dtype", [(65, 65, torch.float32), (50257, 50304, torch.bfloat16), (50257, 50304, torch.float32),
+                                         (1000, 1000, torch.bfloat16)])
+def test_cross_entropy(dev, V, ld, dtype):
+    from penroz import ops
+    torch.manual_seed(V)
+    M = 257
+    buf = torch.zeros(M, ld, device=dev, dtype=dtype)
+    buf[:, :V] = (torch.randn(M, V, device=dev) * 3).to(dtype)
+    tgt = torch.randint(0, V, (M,), device=dev)
+    tgt[5] = -100; tgt[77] = -100
+    lg = buf[:, :V].float().requires_grad_(True)
+    ref = F.cross_entropy(lg, tgt)
+    ref.backward()
+    nv = torch.zeros(1, device=dev, dtype=torch.int32)
+    rows = torch.empty(M, device=dev)
+    loss = torch.zeros(1, device=dev)
+    ops.ce_count_valid(tgt, nv)
+    assert nv.item() == M - 2
+    work = buf.clone()
+    ops.ce_rows(work, tgt, nv, rows, V=V, grad_scale=1.0, write_grad=True)
+    ops.ce_reduce(rows, nv, loss)
+    assert abs(loss.item() - ref.item()) < 2e-5 * max(1.0, abs(ref.item()))
+    g = work[:, :V].float()
+    tol = 1e-5 if dtype == torch.float32 else 8e-3
+    assert rel_err(g, lg.grad) < tol
+    assert g[5].abs().max().item() == 0.0
+    # forward only leaves the logits untouched
+    work2 = buf.clone()
+    ops.ce_rows(work2, tgt, nv, rows, V=V, write_grad=False)
+    assert torch.equal(work2, buf)
+
+
+def test_adamw_and_grad_norm(dev):
+    from penroz import ops
+    torch.manual_seed(5)
+    n = 1_000_003
+    p = torch.randn(n, device=dev); g = torch.randn(n, device=dev) * 0.1
+    ref_p = p.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([ref_p], lr=6e-4, betas=(0.9, 0.95), eps=1e-8, foreach=False, fused=False)
+    m = torch.zeros(n, device=dev); v = torch.zeros(n, device=dev)
+    shadow = torch.empty(n, device=dev, dtype=torch.bfloat16)
+    for step in range(1, 4):
+        gg = g * step
+        ref_p.grad = gg.clone()
+        opt.step()
+        gbuf = gg.clone()
+        ops.adamw_flat(p, gbuf, m, v, shadow, lr=6e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.01, step=step,
+                       zero_grad=True)
+        assert gbuf.abs().max().item() == 0.0
+    st = opt.state[ref_p]
+    # same operation order as torch's single-tensor AdamW: agreement to a few fp32 ulps
+    assert (p - ref_p.detach()).abs().max().item() < 2e-6
+    assert rel_err(m, st["exp_avg"]) < 1e-6
+    assert rel_err(v, st["exp_avg_sq"]) < 1e-6
+    assert torch.equal(shadow, p.bfloat16())
+    norm = torch.zeros(1, device=dev); mult = torch.zeros(1, device=dev)
+    ops.grad_norm(g, 1.0, norm, mult)
+    assert abs(norm.item() - g.double().norm().item()) < 1e-3 * g.norm().item()
+    assert abs(mult.item() - min(1.0, 1.0 / (g.norm().item() + 1e-6))) < 1e-5
+
+
+# ------------------------------------------------------------------ decode kernels
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_decode_kernels(dev, dtype):
+    from penroz import ops, _lib
+    torch.manual_seed(6)
+    B, H, D, Tctx = 3, 4, 64, 200
+    C = H * D
+    PAGE = _lib.lib().kv_page_size()
+    max_pages = (Tctx + 1 + PAGE - 1) // PAGE
+    pool = torch.zeros(B * max_pages, 2, H, PAGE, D, device=dev, dtype=dtype)
+    # scrambled page assignment to exercise the indirection
+    perm = torch.randperm(B * max_pages, device=dev).view(B, max_pages).int().contiguous()
+    hist = torch.randn(B, Tctx, 3 * C, device=dev).to(dtype)
+    ops.kv_append(hist.view(B * Tctx, 3 * C), pool, perm, B, Tctx, H, D, 0)
+    new = torch.randn(B, 3 * C, device=dev).to(dtype)
+    ops.kv_append(new, pool, perm, B, 1, H, D, Tctx)
+    out = ops.attn_decode(new, pool, perm, B, H, D, Tctx + 1)
+    allk = torch.cat([hist[:, :, C:2 * C], new[:, None, C:2 * C]], 1).view(B, Tctx + 1, H, D).transpose(1, 2).float()
+    allv = torch.cat([hist[:, :, 2 * C:], new[:, None, 2 * C:]], 1).view(B, Tctx + 1, H, D).transpose(1, 2).float()
+    q = new[:, :C].view(B, 1, H, D).transpose(1, 2).float()
+    ref = F.scaled_dot_product_attention(q, allk, allv).transpose(1, 2).reshape(B, C)
+    assert rel_err(out, ref) < (1e-5 if dtype == torch.float32 else 8e-3)
+    # skinny linear
+    for M in (1, 3, 11):
+        x = torch.randn(M, 768, device=dev).to(dtype)
+        W = (torch.randn(1000, 768, device=dev) * 0.05).to(dtype)
+        bias = torch.randn(1000, device=dev).to(dtype)
+        ref = x.float() @ W.float().t() + bias.float()
+        o = ops.skinny_linear(x, W, bias)
+        tol = 1e-5 if dtype == torch.float32 else 4e-3
+        assert rel_err(o, ref) < tol
+        og = ops.skinny_linear(x, W, bias, epilogue=1)
+        assert rel_err(og, F.gelu(ref.to(dtype).float())) < tol * 2
+        aux = torch.randn(M, 1000, device=dev).to(dtype)
+        orr = ops.skinny_linear(x, W, bias, epilogue=2, aux=aux)
+        assert rel_err(orr, aux.float() + ref) < tol * 2
+    lg = torch.randn(5, 50304, device=dev).to(dtype)
+    lg[2, 100] = 50.0; lg[2, 40000] = 50.0  # tie -> lowest index
+    am = ops.argmax_rows(lg, V=50257)
+    assert torch.equal(am, lg[:, :50257].float().argmax(dim=-1))
+    assert am[2].item() == 100
