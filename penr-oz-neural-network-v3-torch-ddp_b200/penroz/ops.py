@@ -63,6 +63,7 @@ def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=Non
 
 
 def embed_fwd(idx, wte, wpe, pos_offset=0, out_dtype=None, err_flag=None):
+    idx = idx.contiguous()
     B, T = idx.shape
     V, C = wte.shape
     out_dtype = out_dtype or wte.dtype
@@ -73,6 +74,7 @@ def embed_fwd(idx, wte, wpe, pos_offset=0, out_dtype=None, err_flag=None):
 
 
 def embed_bwd(idx, dx, dwte, dwpe, pos_offset=0):
+    idx = idx.contiguous()
     B, T = idx.shape
     V, C = dwte.shape
     lib().embed_bwd(ptr(idx), ptr(dx), ptr(dwte), ptr(dwpe), B, T, C, V, pos_offset, stream())
