@@ -62,12 +62,14 @@ def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=Non
     return (out, out2) if epilogue == EPI_GELU else out
 
 
-def embed_fwd(idx, wte, wpe, pos_offset=0, out_dtype=None, err_flag=None):
+def embed_fwd(idx, wte, wpe, pos_offset=0, out_dtype=None, err_flag=None, out=None):
     idx = idx.contiguous()
     B, T = idx.shape
     V, C = wte.shape
-    out_dtype = out_dtype or wte.dtype
-    out = torch.empty((B, T, C), device=idx.device, dtype=out_dtype)
+    if out is None:
+        out_dtype = out_dtype or wte.dtype
+        out = torch.empty((B, T, C), device=idx.device, dtype=out_dtype)
+    out_dtype = out.dtype
     lib().embed_fwd(ptr(idx), ptr(wte), ptr(wpe), ptr(out), B, T, C, V, pos_offset, dt(wte),
                     F32 if out_dtype == torch.float32 else BF16, ptr(err_flag), stream())
     return out
@@ -80,13 +82,16 @@ def embed_bwd(idx, dx, dwte, dwpe, pos_offset=0):
     lib().embed_bwd(ptr(idx), ptr(dx), ptr(dwte), ptr(dwpe), B, T, C, V, pos_offset, stream())
 
 
-def layernorm_fwd(x, gamma, beta, eps=1e-5, out_dtype=None, save_stats=True):
+def layernorm_fwd(x, gamma, beta, eps=1e-5, out_dtype=None, save_stats=True, out=None, mean=None, rstd=None):
     C = x.shape[-1]
     rows = x.numel() // C
-    out_dtype = out_dtype or x.dtype
-    out = torch.empty(x.shape, device=x.device, dtype=out_dtype)
-    mean = torch.empty(rows, device=x.device, dtype=torch.float32) if save_stats else None
-    rstd = torch.empty(rows, device=x.device, dtype=torch.float32) if save_stats else None
+    if out is None:
+        out_dtype = out_dtype or x.dtype
+        out = torch.empty(x.shape, device=x.device, dtype=out_dtype)
+    out_dtype = out.dtype
+    if save_stats and mean is None:
+        mean = torch.empty(rows, device=x.device, dtype=torch.float32)
+        rstd = torch.empty(rows, device=x.device, dtype=torch.float32)
     lib().layernorm_fwd(ptr(x), ptr(gamma), ptr(beta), ptr(out), ptr(mean), ptr(rstd), rows, C, eps, dt(x), dt(gamma),
                         F32 if out_dtype == torch.float32 else BF16, stream())
     return out, mean, rstd
@@ -98,12 +103,16 @@ def layernorm_bwd_scratch(rows, C, device):
 
 
 def layernorm_bwd(dy, x, gamma, mean, rstd, *, add=None, dgamma=None, dbeta=None, dcol=None, want_bf16=False,
-                  scratch=None):
+                  scratch=None, dx=None, dxb=None):
     """Returns (dx, dx_bf16|None); accumulates (+=) into dgamma/dbeta/dcol."""
     C = x.shape[-1]
     rows = x.numel() // C
-    dx = torch.empty_like(x)
-    dxb = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16) if want_bf16 else None
+    if dx is None:
+        dx = torch.empty_like(x)
+    if want_bf16 and dxb is None:
+        dxb = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    if not want_bf16:
+        dxb = None
     if scratch is None:
         scratch = layernorm_bwd_scratch(rows, C, x.device)
     lib().layernorm_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(mean), ptr(rstd), ptr(add), ptr(dx), ptr(dxb), ptr(dgamma),
@@ -138,21 +147,24 @@ def cast(src, dst):
     return dst
 
 
-def attn_fwd(qkv, H, want_lse=True):
+def attn_fwd(qkv, H, want_lse=True, out=None, lse=None):
     """qkv [B,T,3C] -> (out [B,T,C], lse [B,H,T])."""
     B, T, C3 = qkv.shape
     C = C3 // 3
     D = C // H
-    out = torch.empty((B, T, C), device=qkv.device, dtype=qkv.dtype)
-    lse = torch.empty((B, H, T), device=qkv.device, dtype=torch.float32) if want_lse else None
+    if out is None:
+        out = torch.empty((B, T, C), device=qkv.device, dtype=qkv.dtype)
+    if want_lse and lse is None:
+        lse = torch.empty((B, H, T), device=qkv.device, dtype=torch.float32)
     lib().attn_fwd_simt(ptr(qkv), ptr(out), ptr(lse), B, T, H, D, dt(qkv), stream())
     return out, lse
 
 
-def attn_bwd(qkv, out, dout, lse, H, scratch=None):
+def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None):
     B, T, C3 = qkv.shape
     D = (C3 // 3) // H
-    dqkv = torch.empty_like(qkv)
+    if dqkv is None:
+        dqkv = torch.empty_like(qkv)
     if scratch is None:
         scratch = torch.empty(lib().attn_bwd_scratch_bytes(B, T, H), device=qkv.device, dtype=torch.uint8)
     lib().attn_bwd_simt(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, dt(qkv), ptr(scratch),
