@@ -121,7 +121,8 @@ class NeuralNetworkModel(nn.Module):
             return None
         if self._fused is None or self._fused.device != first.device:
             from penroz.engine import Gpt2Engine
-            self._fused = Gpt2Engine(self._plan, list(self.parameters()), self.optimizer)
+            with torch.inference_mode(False):  # engine-owned tensors must outlive an inference_mode() caller
+                self._fused = Gpt2Engine(self._plan, list(self.parameters()), self.optimizer)
         return self._fused
 
     def _maybe_accelerate(self):
