@@ -238,7 +238,8 @@ def run_ours(args):
     B, T, V = cfg["B"], cfg["T"], cfg["V"]
     work = tempfile.mkdtemp(prefix=f"penroz_bench_r{rank}_")
     os.chdir(work)
-    nnm.NeuralNetworkModel.SHM_PATH = work
+    nnm.NeuralNetworkModel.SHM_PATH = os.path.join(work, "shm")
+    os.makedirs(nnm.NeuralNetworkModel.SHM_PATH, exist_ok=True)
     model = build_model()
     model.to("cuda")
     eng = model._engine()
