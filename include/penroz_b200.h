@@ -94,6 +94,26 @@ size_t penroz_colsum_scratch_bytes(int M, int N);
 int penroz_colsum(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype, void* scratch,
                   size_t scratch_bytes, void* stream);
 
+/* ---- column sums with no caller scratch and no allocation: out[n] (+)= sum_m X[m,n], N <= 8192 ----
+ * No counterpart in the reference (it is a variant of penroz_colsum added for this library's own callers).
+ * Who needs it: a host that binds this C ABI from outside PyTorch — for example the reference service's worker
+ * calling through a ctypes/cffi stub — receives device pointers for inputs and outputs from its framework but owns
+ * no device allocator; and inside a training worker PyTorch's caching allocator has usually reserved almost all of
+ * HBM, so a raw cudaMalloc from such a host can fail (or stall the device while it synchronises) even though plenty
+ * of memory is "free" inside torch. For those callers the partial-sum buffer is a fixed 1 MiB array (32 x 8192
+ * floats) that is part of the library image: every GPU that loads the library holds it until the process exits.
+ *   - N > PENROZ_COLSUM_STATIC_MAX_COLS is rejected with PENROZ_ERR_LIMIT; use penroz_colsum for wider matrices.
+ *   - The first call on each device looks up the array's device address (one cudaGetSymbolAddress, that device
+ *     current) and remembers it; make that first call before starting any stream capture. Later calls only launch.
+ *   - The call never allocates or frees: no cudaMalloc/cudaFree, no library routine that allocates.
+ *   - All calls on a device share the one array and it keeps whatever the previous call left in it. Each call
+ *     overwrites every slot it later reads, so stale contents are harmless, but two calls whose kernels overlap on
+ *     the GPU (different streams, or different host threads on different streams) race on it: issue them on one
+ *     stream, or order them with events. */
+#define PENROZ_COLSUM_STATIC_MAX_COLS 8192
+int penroz_colsum_static(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype,
+                         void* stream);
+
 /* ---- dtype cast of a flat buffer (autocast's per-step weight cast, done once per optimizer step here) ---- */
 int penroz_cast(const void* in, void* out, long long n, int in_dtype, int out_dtype, void* stream);
 

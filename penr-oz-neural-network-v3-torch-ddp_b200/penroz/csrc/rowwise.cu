@@ -510,3 +510,63 @@ extern "C" int penroz_cast(const void* in, void* out, long long n, int in_dtype,
     count_launch();
     return check_launch("cast");
 }
+
+// ------------------------------------------------------------------ column sums without caller scratch
+// Same two kernels as penroz_colsum, but the [32][N] partial-sum buffer lives in a fixed array inside the library
+// image instead of being passed in. It exists for hosts that hand this library nothing but input and output
+// pointers and cannot obtain device memory themselves (see the header comment of penroz_colsum_static).
+namespace penroz {
+constexpr int kStaticColsumMaxCols = 8192;   // == PENROZ_COLSUM_STATIC_MAX_COLS in include/penroz_b200.h
+constexpr int kStaticColsumParts = 32;
+// 32 x 8192 floats = 1 MiB of global memory on every GPU that loads the library, held until the process exits.
+static __device__ __align__(256) float g_colsum_static_scratch[kStaticColsumParts * kStaticColsumMaxCols];
+
+// Device address of the array above for the CURRENT device, resolved once per device. In host code the symbol
+// name is only a handle (its host-side value is not a device address), so kernels are always given the pointer
+// that cudaGetSymbolAddress returns, never the name.
+static int static_colsum_scratch(float** out) {
+    static std::atomic<float*> resolved[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { set_error("colsum_static: cudaGetDevice: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+    if (dev < 0 || dev >= 64) { set_error("colsum_static: device ordinal %d not supported", dev); return PENROZ_ERR_LIMIT; }
+    float* p = resolved[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        void* addr = nullptr;
+        e = cudaGetSymbolAddress(&addr, g_colsum_static_scratch);
+        if (e != cudaSuccess || addr == nullptr) {
+            set_error("colsum_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return PENROZ_ERR_CUDA;
+        }
+        p = static_cast<float*>(addr);
+        resolved[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return PENROZ_OK;
+}
+}  // namespace penroz
+
+extern "C" int penroz_colsum_static(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype,
+                                    void* stream) {
+    PENROZ_REQUIRE(M > 0 && N > 0, "colsum_static: bad shape M=%d N=%d", M, N);
+    PENROZ_REQUIRE(X != nullptr && out != nullptr, "colsum_static: null argument");
+    PENROZ_REQUIRE(ld % 4 == 0, "colsum_static: ld must be a multiple of 4");
+    if (N > kStaticColsumMaxCols) {
+        set_error("colsum_static: N=%d exceeds the built-in scratch (at most %d columns); use penroz_colsum with "
+                  "caller-provided scratch for wider matrices", N, kStaticColsumMaxCols);
+        return PENROZ_ERR_LIMIT;
+    }
+    float* scratch = nullptr;
+    int rc = static_colsum_scratch(&scratch);
+    if (rc != PENROZ_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 g((N + 127) / 128, kStaticColsumParts);
+    // every [part][column < N] slot is written by the first kernel before the second reads it, so nothing left over
+    // from an earlier call is ever consumed and no clearing is needed
+    if (dtype == F32) colsum_partial_kernel<float><<<g, 256, 0, st>>>((const float*)X, ld, M, N, scratch);
+    else if (dtype == BF16) colsum_partial_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)X, ld, M, N, scratch);
+    else { set_error("colsum_static: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
+    colsum_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>(scratch, kStaticColsumParts, N, out, accumulate);
+    count_launch(2);
+    return check_launch("colsum_static");
+}
