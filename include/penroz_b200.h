@@ -125,6 +125,14 @@ size_t penroz_attn_bwd_scratch_bytes(int B, int T, int H);
 int penroz_attn_bwd_simt(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int B,
                          int T, int H, int D, int dtype, void* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- the same attention on the tensor cores (bf16, head_dim 64): tcgen05.mma with S / dP / dK / dV / dQ in TMEM,
+ * q, k, v and dO tiles fetched from the packed buffers by TMA. Replaces the same reference lines as above for the
+ * bf16-autocast training step. The backward needs scratch (row dot-products + an fp32 dQ accumulator it zeroes). */
+int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
+size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D);
+int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int B, int T,
+                       int H, int D, void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- softmax cross-entropy over a chunk of logits rows ----
  * Replaces F.cross_entropy(logits.view(-1,V), target.view(-1)) (neural_net_model.py:264-267): mean over rows whose
  * target != ignore_index. ce_rows writes per-row losses and (write_grad) overwrites the logits rows in place with

@@ -232,6 +232,250 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
     if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+// ---------------------------------------------------------------------------------------------- backward
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (one warp per (row, head))
+__global__ void attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
+                                      float* __restrict__ delta, int rows, int Tn, int H) {
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (gw >= rows * H) return;
+    const int row = gw / H, h = gw % H;
+    const size_t off = (size_t)row * H * AT_D + h * AT_D + lane * 2;
+    const float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(o + off));
+    const float2 g = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(dout + off));
+    const float s = warp_sum(a.x * g.x + a.y * g.y);
+    if (lane == 0) delta[((size_t)(row / Tn) * H + h) * Tn + (row % Tn)] = s;
+}
+
+// dq_accum (fp32 [rows, C]) -> bf16 into the q third of dqkv [rows, 3C]
+__global__ void attn_bwd_dq_finish_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, size_t rows,
+                                          int C) {
+    const size_t n4 = rows * (size_t)C / 4;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = reinterpret_cast<const float4*>(acc)[i];
+        const size_t e = i * 4, r = e / C, c = e % C;
+        uint2 w;
+        w.x = pack_bf16x2(v.x, v.y);
+        w.y = pack_bf16x2(v.z, v.w);
+        *reinterpret_cast<uint2*>(dqkv + r * 3 * (size_t)C + c) = w;
+    }
+}
+
+struct AttnBwdSmem {
+    static constexpr int kK = 0;                       // 16 KB   K_j  [128 keys][64]
+    static constexpr int kV = 16384;                   // 16 KB   V_j
+    static constexpr int kQ0 = 32768;                  // 2 x 16 KB  Q_i
+    static constexpr int kG0 = kQ0 + 2 * 16384;        // 2 x 16 KB  dO_i
+    static constexpr int kP = kG0 + 2 * 16384;         // 32 KB  P   [2 key blocks][128 q][64]
+    static constexpr int kDS = kP + 32768;             // 32 KB  dS  same layout
+    static constexpr int kBar = kDS + 32768;
+    static constexpr int kBytes = kBar + 128 + 1024;
+};
+
+__global__ void __launch_bounds__(192, 1)
+attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                   const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
+                   __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2e) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
+    uint8_t* smem = smem_raw + pad;
+    const uint32_t sbase = raw + pad;
+    const uint32_t bar = sbase + AttnBwdSmem::kBar;
+    const uint32_t kv_full = bar, qg_full0 = bar + 8, qg_empty0 = bar + 24, sdp_full = bar + 40, pds_ready = bar + 48,
+                   dq_full = bar + 56;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + AttnBwdSmem::kBar + 64);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_qt = (Tn + AT_BM - 1) / AT_BM;
+    const int jt = blockIdx.x;                         // key tile; tile 0 has the most query tiles -> scheduled first
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int C = H * AT_D;
+    const int n_it = n_qt - jt;                        // query tiles jt .. n_qt-1
+
+    if (threadIdx.x == 128) {
+        tma_prefetch_desc(&tmQKV);
+        tma_prefetch_desc(&tmDO);
+        mbar_init(kv_full, 1);
+        mbar_init(qg_full0, 1); mbar_init(qg_full0 + 8, 1);
+        mbar_init(qg_empty0, 1); mbar_init(qg_empty0 + 8, 1);
+        mbar_init(sdp_full, 1);
+        mbar_init(pds_ready, 4);
+        mbar_init(dq_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) {
+        tmem_alloc(smem_u32(tmem_slot), 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 320, tDQ = tmem + 384;
+
+    if (warp == 5) {
+        // ------------------------------------------------ TMA producer
+        if (lane == 0) {
+            mbar_expect_tx(kv_full, 32768);
+            tma_load_2d(sbase + AttnBwdSmem::kK, &tmQKV, kv_full, C + h * AT_D, b * Tn + jt * AT_BN);
+            tma_load_2d(sbase + AttnBwdSmem::kV, &tmQKV, kv_full, 2 * C + h * AT_D, b * Tn + jt * AT_BN);
+            for (int it = 0; it < n_it; ++it) {
+                const int s = it & 1;
+                if (it >= 2) mbar_wait(qg_empty0 + 8 * s, (uint32_t)(((it - 2) >> 1) & 1));
+                const int qrow = b * Tn + (jt + it) * AT_BM;
+                mbar_expect_tx(qg_full0 + 8 * s, 32768);
+                tma_load_2d(sbase + AttnBwdSmem::kQ0 + s * 16384, &tmQKV, qg_full0 + 8 * s, h * AT_D, qrow);
+                tma_load_2d(sbase + AttnBwdSmem::kG0 + s * 16384, &tmDO, qg_full0 + 8 * s, h * AT_D, qrow);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 4) {
+        // ------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            const uint32_t sK = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV;
+            const uint32_t sP = sbase + AttnBwdSmem::kP, sDS = sbase + AttnBwdSmem::kDS;
+            const uint32_t id_kk128 = at_idesc(0, 0, 128);   // A K-major, B K-major, N=128  (S, dP)
+            const uint32_t id_mm64 = at_idesc(1, 1, 64);     // A MN-major, B MN-major, N=64 (dV, dK)
+            const uint32_t id_km64 = at_idesc(0, 1, 64);     // A K-major, B MN-major, N=64  (dQ)
+            mbar_wait(kv_full, 0);
+            for (int it = 0; it < n_it; ++it) {
+                const int s = it & 1;
+                const uint32_t sQ = sbase + AttnBwdSmem::kQ0 + s * 16384;
+                const uint32_t sG = sbase + AttnBwdSmem::kG0 + s * 16384;
+                mbar_wait(qg_full0 + 8 * s, (uint32_t)((it >> 1) & 1));
+                tc_fence_after();
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4)   // S = Q K^T
+                    umma_bf16(tS, at_desc(sQ + k4 * 32, 1, 64), at_desc(sK + k4 * 32, 1, 64), id_kk128, (uint32_t)(k4 != 0));
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4)   // dP = dO V^T
+                    umma_bf16(tDP, at_desc(sG + k4 * 32, 1, 64), at_desc(sV + k4 * 32, 1, 64), id_kk128, (uint32_t)(k4 != 0));
+                umma_commit(sdp_full);
+                mbar_wait(pds_ready, (uint32_t)(it & 1));
+                tc_fence_after();
+#pragma unroll
+                for (int k8 = 0; k8 < 8; ++k8)   // dV += P^T dO   (M = keys, K = queries)
+                    umma_bf16(tDV, at_desc(sP + k8 * 2048, 1024, 64), at_desc(sG + k8 * 2048, 512, 64), id_mm64,
+                              (uint32_t)((it | k8) != 0));
+#pragma unroll
+                for (int k8 = 0; k8 < 8; ++k8)   // dK += dS^T Q
+                    umma_bf16(tDK, at_desc(sDS + k8 * 2048, 1024, 64), at_desc(sQ + k8 * 2048, 512, 64), id_mm64,
+                              (uint32_t)((it | k8) != 0));
+#pragma unroll
+                for (int k8 = 0; k8 < 8; ++k8)   // dQ_i = dS K   (M = queries, K = keys)
+                    umma_bf16(tDQ, at_desc(sDS + (k8 >> 2) * 16384 + (k8 & 3) * 32, 1, 64), at_desc(sK + k8 * 2048, 512, 64),
+                              id_km64, (uint32_t)(k8 != 0));
+                umma_commit(dq_full);
+                umma_commit(qg_empty0 + 8 * s);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ------------------------------------------------ softmax-gradient threads: one query row (TMEM lane) each
+        const int r = warp * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+        uint8_t* sPp = smem + AttnBwdSmem::kP;
+        uint8_t* sDSp = smem + AttnBwdSmem::kDS;
+        const float log2e = 1.44269504088896340736f;
+        for (int it = 0; it < n_it; ++it) {
+            const int qt = jt + it;
+            const int i = qt * AT_BM + r;               // query position
+            const bool row_ok = i < Tn;
+            const size_t stat = ((size_t)b * H + h) * Tn + (row_ok ? i : 0);
+            const float L2 = row_ok ? lse[stat] * log2e : 0.f;
+            const float dl = row_ok ? delta[stat] : 0.f;
+            const bool diag = (it == 0);
+            const int key0 = jt * AT_BN;
+            mbar_wait(sdp_full, (uint32_t)(it & 1));
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t sv[32], dv[32];
+                tmem_ld_32x32(tS + lane_addr + c * 32, sv);
+                tmem_ld_32x32(tDP + lane_addr + c * 32, dv);
+                tmem_ld_wait();
+                uint32_t pp[16], dd[16];
+#pragma unroll
+                for (int k = 0; k < 32; k += 2) {
+                    float p0 = exp2f(__uint_as_float(sv[k]) * scale_log2e - L2);
+                    float p1 = exp2f(__uint_as_float(sv[k + 1]) * scale_log2e - L2);
+                    if (!row_ok || (diag && key0 + c * 32 + k > i)) p0 = 0.f;
+                    if (!row_ok || (diag && key0 + c * 32 + k + 1 > i)) p1 = 0.f;
+                    const float d0 = p0 * (__uint_as_float(dv[k]) - dl) * scale;
+                    const float d1 = p1 * (__uint_as_float(dv[k + 1]) - dl) * scale;
+                    pp[k >> 1] = pack_bf16x2(p0, p1);
+                    dd[k >> 1] = pack_bf16x2(d0, d1);
+                }
+                uint8_t* pb = sPp + (c >> 1) * 16384;
+                uint8_t* db = sDSp + (c >> 1) * 16384;
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4) {
+                    const uint32_t off = sw128_off(r, (c & 1) * 32 + q4 * 8);
+                    *reinterpret_cast<uint4*>(pb + off) = make_uint4(pp[4 * q4], pp[4 * q4 + 1], pp[4 * q4 + 2], pp[4 * q4 + 3]);
+                    *reinterpret_cast<uint4*>(db + off) = make_uint4(dd[4 * q4], dd[4 * q4 + 1], dd[4 * q4 + 2], dd[4 * q4 + 3]);
+                }
+            }
+            tc_fence_before();
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(pds_ready);
+            mbar_wait(dq_full, (uint32_t)(it & 1));
+            tc_fence_after();
+            float* dq = dq_accum + ((size_t)(b * Tn) + (row_ok ? i : 0)) * C + h * AT_D;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t v[32];
+                __syncwarp();
+                tmem_ld_32x32(tDQ + lane_addr + c * 32, v);
+                tmem_ld_wait();
+                if (row_ok) {
+#pragma unroll
+                    for (int k = 0; k < 32; k += 4)
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq + c * 32 + k),
+                                     "f"(__uint_as_float(v[k])), "f"(__uint_as_float(v[k + 1])),
+                                     "f"(__uint_as_float(v[k + 2])), "f"(__uint_as_float(v[k + 3]))
+                                     : "memory");
+                }
+            }
+            __syncwarp();
+            tc_fence_before();
+        }
+        // dV, dK of this key tile: lane = key row
+        const int key = jt * AT_BN + r;
+        const bool key_ok = key < Tn;
+        __nv_bfloat16* gk = dqkv + ((size_t)(b * Tn) + (key_ok ? key : 0)) * 3 * C + C + h * AT_D;
+        __nv_bfloat16* gv = gk + C;
+#pragma unroll 1
+        for (int which = 0; which < 2; ++which) {
+            const uint32_t taddr = which == 0 ? tDV : tDK;
+            __nv_bfloat16* dst = which == 0 ? gv : gk;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t v[32];
+                __syncwarp();
+                tmem_ld_32x32(taddr + lane_addr + c * 32, v);
+                tmem_ld_wait();
+                if (key_ok) {
+#pragma unroll
+                    for (int k = 0; k < 32; k += 8) {
+                        uint4 w;
+                        w.x = pack_bf16x2(__uint_as_float(v[k]), __uint_as_float(v[k + 1]));
+                        w.y = pack_bf16x2(__uint_as_float(v[k + 2]), __uint_as_float(v[k + 3]));
+                        w.z = pack_bf16x2(__uint_as_float(v[k + 4]), __uint_as_float(v[k + 5]));
+                        w.w = pack_bf16x2(__uint_as_float(v[k + 6]), __uint_as_float(v[k + 7]));
+                        *reinterpret_cast<uint4*>(dst + c * 32 + k) = w;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFnA)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -285,4 +529,51 @@ extern "C" int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B,
     attn_fwd_tc_kernel<<<grid, 160, AttnFwdSmem::kBytes, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, scale_log2e);
     count_launch();
     return check_launch("attn_fwd_tc");
+}
+
+extern "C" size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D) {
+    return ((((size_t)B * H * T + 3) / 4) * 4 + (size_t)B * T * H * D) * sizeof(float);
+}
+
+// dqkv [B,T,3C] <- gradient of causal attention wrt the packed QKV buffer. scratch: delta [B,H,T] + dq accumulator
+// [B*T, C] fp32 (zeroed here with cudaMemsetAsync on `stream`).
+extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                  int B, int T, int H, int D, void* scratch, size_t scratch_bytes, void* stream) {
+    PENROZ_REQUIRE(B > 0 && T > 0 && H > 0, "attn_bwd_tc: bad shape");
+    PENROZ_REQUIRE(D == 64, "attn_bwd_tc: head_dim %d unsupported (tensor-core path is head_dim 64)", D);
+    PENROZ_REQUIRE(B <= 65535 && H <= 65535, "attn_bwd_tc: B/H too large for the launch grid");
+    PENROZ_REQUIRE(scratch && scratch_bytes >= penroz_attn_bwd_tc_scratch_bytes(B, T, H, D), "attn_bwd_tc: scratch too small");
+    PENROZ_REQUIRE(((uintptr_t)qkv % 16 == 0) && ((uintptr_t)dout % 16 == 0) && ((uintptr_t)dqkv % 16 == 0) &&
+                   ((uintptr_t)scratch % 16 == 0), "attn_bwd_tc: buffers must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int C = H * D;
+    const size_t rows = (size_t)B * T;
+    float* delta = (float*)scratch;
+    float* dq_acc = delta + (((size_t)B * H * T + 3) / 4) * 4;
+    CUtensorMap tmQ, tmG;
+    int rc = encode_rows_bf16(&tmQ, qkv, (uint64_t)3 * C, rows, 128);
+    if (rc) return rc;
+    rc = encode_rows_bf16(&tmG, dout, (uint64_t)C, rows, 128);
+    if (rc) return rc;
+    static std::atomic<int> configured{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!((configured.load() >> dev) & 1)) {
+        cudaError_t e = cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnBwdSmem::kBytes);
+        if (e != cudaSuccess) { set_error("attn_bwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+        configured.fetch_or(1 << dev);
+    }
+    cudaError_t e = cudaMemsetAsync(dq_acc, 0, rows * C * sizeof(float), st);
+    if (e != cudaSuccess) { set_error("attn_bwd_tc: memset: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+    const long long warps = (long long)rows * H;
+    attn_bwd_delta_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
+    dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
+    const float scale = 1.0f / sqrtf((float)D);
+    attn_bwd_tc_kernel<<<grid, 192, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
+    size_t n4 = rows * C / 4;
+    size_t g = (n4 + 255) / 256;
+    size_t cap = (size_t)num_sms() * 16;
+    attn_bwd_dq_finish_kernel<<<(unsigned)(g > cap ? cap : g), 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, C);
+    count_launch(3);
+    return check_launch("attn_bwd_tc");
 }

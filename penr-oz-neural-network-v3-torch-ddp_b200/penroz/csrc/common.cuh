@@ -128,6 +128,46 @@ __device__ __forceinline__ float gelu_tanh_grad(float x) {
     return 0.5f * (1.f + t) + 0.5f * x * dt;
 }
 
+// Branch-free variants for the tensor-core epilogues, whose outputs are rounded to bf16 (2^-9 relative): erf by
+// Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7), exp/reciprocal/tanh on the SFU. No branches, so the 32 independent
+// elements a thread holds pipeline instead of serialising on erff's control flow.
+__device__ __forceinline__ float erf_and_gauss_fast(float z, float& gauss) {   // z >= 0 handled by the callers' sign fix
+    const float az = fabsf(z);
+    const float t = __frcp_rn(fmaf(0.3275911f, az, 1.f));
+    gauss = __expf(-az * az);
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float e = fmaf(-poly * t, gauss, 1.f);
+    return copysignf(e, z);
+}
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+    float g;
+    return 0.5f * x * (1.f + erf_and_gauss_fast(x * 0.70710678118654752440f, g));
+}
+__device__ __forceinline__ float gelu_erf_grad_fast(float x) {
+    float g;   // g = exp(-x^2/2)
+    const float cdf = 0.5f * (1.f + erf_and_gauss_fast(x * 0.70710678118654752440f, g));
+    return fmaf(x * 0.39894228040143267794f, g, cdf);
+}
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float gelu_tanh_fast(float x) {
+    const float k = 0.79788456080286535588f, c = 0.044715f;
+    return 0.5f * x * (1.f + tanh_fast(k * (x + c * x * x * x)));
+}
+__device__ __forceinline__ float gelu_tanh_grad_fast(float x) {
+    const float k = 0.79788456080286535588f, c = 0.044715f;
+    const float x2 = x * x;
+    const float t = tanh_fast(k * (x + c * x * x2));
+    const float dt = (1.f - t * t) * k * (1.f + 3.f * c * x2);
+    return 0.5f * (1.f + t) + 0.5f * x * dt;
+}
+
 // ---------------------------------------------------------------- sm_100a PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

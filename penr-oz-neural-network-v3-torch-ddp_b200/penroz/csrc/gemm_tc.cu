@@ -5,11 +5,12 @@
 // neural_net_model.py:250-258 runs them; .backward() at neural_net_model.py:650-653).
 //
 // Design (B200 / sm_100a):
-//   * persistent, warp-specialised CTA (256 threads, one CTA per SM):
+//   * persistent, warp-specialised CTA (384 threads, one CTA per SM):
 //       warp 0  TMA producer   (cp.async.bulk.tensor 2D, 128B swizzle, mbarrier complete_tx)
 //       warp 1  MMA issuer     (one elected lane issues tcgen05.mma cta_group::1 kind::f16, M=128 N=BN K=16)
 //       warp 2  TMEM allocator
-//       warps 4-7 epilogue     (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+//       warps 4-11 epilogue    (tcgen05.ld 32x32b -> registers -> fused epilogue -> global; lane quarter = warp % 4,
+//                               column half = (warp - 4) / 4)
 //   * smem ring of kStages x {A 128x64, B BNx64} bf16 tiles, full/empty mbarriers
 //   * TMEM double buffered (2 x BN fp32 columns) so the epilogue of tile i overlaps the MMAs of tile i+1
 //   * both operands may be K-major (row-major [rows,K]) or MN-major (row-major [K,rows]); MN-major is what
@@ -65,7 +66,7 @@ template <int BN> struct GemmCfg {
 };
 
 template <int BN, int EPI>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(384, 1)
 gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmParams p) {
     using Cfg = GemmCfg<BN>;
@@ -96,7 +97,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
-            mbar_init(tempty_bar(s), 4);
+            mbar_init(tempty_bar(s), 8);
         }
         mbar_fence_init();
     }
@@ -190,8 +191,11 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (as == 0) aph ^= 1u;
         }
     } else if (warp >= 4) {
-        // ------------------------------------------------------------ epilogue (warps 4..7 -> TMEM lane quarters 0..3)
-        const int q = warp - 4;
+        // ------------------------------------------------------------ epilogue: 8 warps. TMEM lane quarter = warp % 4
+        // (hardware rule), column half = (warp - 4) / 4: two warps per SM sub-partition hide each other's latency.
+        const int q = warp & 3;
+        const int half = (warp - 4) >> 2;
+        constexpr int kChunks = BN / 64;   // 32-column chunks per warp
         int as = 0;
         uint32_t aph = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -203,7 +207,8 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < p.M;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int cc = 0; cc < kChunks; ++cc) {
+                const int c = half * kChunks + cc;
                 uint32_t v[32];
                 __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the predicated stores below
                 tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
@@ -215,9 +220,19 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
                 if (EPI != EPI_ACCUM_F32 && EPI != EPI_DGELU && p.bias != nullptr) {
+                    if (full && ((col0 & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0)) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (full || col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
+                        for (int j = 0; j < 4; ++j) {   // same 16 B for every lane: one broadcast request
+                            const uint4 w = *reinterpret_cast<const uint4*>(p.bias + col0 + 8 * j);
+                            const float2 b0 = unpack_bf16x2(w.x), b1 = unpack_bf16x2(w.y), b2 = unpack_bf16x2(w.z), b3 = unpack_bf16x2(w.w);
+                            acc[8 * j + 0] += b0.x; acc[8 * j + 1] += b0.y; acc[8 * j + 2] += b1.x; acc[8 * j + 3] += b1.y;
+                            acc[8 * j + 4] += b2.x; acc[8 * j + 5] += b2.y; acc[8 * j + 6] += b3.x; acc[8 * j + 7] += b3.y;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (full || col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
+                    }
                 }
                 if (!row_ok) {
                     // rows past M (TMA zero-filled): nothing to store
@@ -228,10 +243,22 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     float r[32], r2[32];
                     if (EPI == EPI_DGELU) {
                         const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (long long)row * p.ldaux + col0;
+                        float hv[32];
+                        if (full && (p.ldaux % 8 == 0)) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const uint4 w = reinterpret_cast<const uint4*>(h)[j];
+                                const float2 h0 = unpack_bf16x2(w.x), h1 = unpack_bf16x2(w.y), h2 = unpack_bf16x2(w.z), h3 = unpack_bf16x2(w.w);
+                                hv[8 * j + 0] = h0.x; hv[8 * j + 1] = h0.y; hv[8 * j + 2] = h1.x; hv[8 * j + 3] = h1.y;
+                                hv[8 * j + 4] = h2.x; hv[8 * j + 5] = h2.y; hv[8 * j + 6] = h3.x; hv[8 * j + 7] = h3.y;
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) hv[i] = (full || col0 + i < p.N) ? __bfloat162float(h[i]) : 0.f;
+                        }
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
-                            float hv = (full || col0 + i < p.N) ? __bfloat162float(h[i]) : 0.f;
-                            float g = p.gelu_tanh ? gelu_tanh_grad(hv) : gelu_erf_grad(hv);
+                            const float g = p.gelu_tanh ? gelu_tanh_grad_fast(hv[i]) : gelu_erf_grad_fast(hv[i]);
                             r[i] = bf16_round(acc[i]) * g;
                         }
                     } else {
@@ -239,8 +266,8 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         for (int i = 0; i < 32; ++i) {
                             r[i] = acc[i];
                             if (EPI == EPI_GELU) {
-                                float pre = bf16_round(acc[i]);
-                                r2[i] = p.gelu_tanh ? gelu_tanh(pre) : gelu_erf(pre);
+                                const float pre = bf16_round(acc[i]);
+                                r2[i] = p.gelu_tanh ? gelu_tanh_fast(pre) : gelu_erf_fast(pre);
                             }
                         }
                     }
@@ -255,6 +282,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             reinterpret_cast<uint4*>(o)[j] = w;
                         }
                     } else {
+#pragma unroll
                         for (int i = 0; i < 32; ++i)
                             if (col0 + i < p.N) o[i] = __float2bfloat16_rn(r[i]);
                     }
@@ -270,6 +298,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                 reinterpret_cast<uint4*>(o2)[j] = w;
                             }
                         } else {
+#pragma unroll
                             for (int i = 0; i < 32; ++i)
                                 if (col0 + i < p.N) o2[i] = __float2bfloat16_rn(r2[i]);
                         }
@@ -296,6 +325,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             reinterpret_cast<float4*>(o)[j] = w;
                         }
                     } else {
+#pragma unroll
                         for (int i = 0; i < 32; ++i)
                             if (col0 + i < p.N)
                                 o[i] = (EPI == EPI_RESID_F32) ? x[i] + bf16_round(acc[i]) : acc[i];
@@ -303,6 +333,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 } else if (EPI == EPI_RESID_BF16) {
                     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * p.ldo + col0;
                     const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (long long)row * p.ldaux + col0;
+#pragma unroll
                     for (int i = 0; i < 32; ++i)
                         if (full || col0 + i < p.N)
                             o[i] = __float2bfloat16_rn(__bfloat162float(x[i]) + bf16_round(acc[i]));
@@ -317,6 +348,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                              "f"(acc[4 * j + 3])
                                              : "memory");
                         } else {
+#pragma unroll
                             for (int i = 0; i < 32; ++i)
                                 if (col0 + i < p.N) atomicAdd(o + i, acc[i]);
                         }
@@ -331,6 +363,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             reinterpret_cast<float4*>(o)[j] = w;
                         }
                     } else {
+#pragma unroll
                         for (int i = 0; i < 32; ++i)
                             if (col0 + i < p.N) o[i] = p.beta ? o[i] + acc[i] : acc[i];
                     }
@@ -343,6 +376,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (as == 0) aph ^= 1u;
         }
     }
+
 
     tc_fence_before();
     __syncthreads();
@@ -398,7 +432,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
         if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
         configured.fetch_or(1 << dev);
     }
-    kern<<<grid, 256, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
+    kern<<<grid, 384, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
     count_launch();
     return check_launch("gemm_bf16_tc");
 }

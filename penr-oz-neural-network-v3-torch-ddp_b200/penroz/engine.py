@@ -419,7 +419,7 @@ class Gpt2Engine:
     def _scratch(self, M, widest):
         C, H = self.plan.n_embd, self.plan.n_head
         need = max(ops.lib().layernorm_bwd_scratch_bytes(M, C), ops.lib().colsum_scratch_bytes(M, widest),
-                   M * H * 4)
+                   M * H * 4 + M * C * 4 + 64)  # attention backward: row dot-products + fp32 dQ accumulator
         return self._buf("scratch", (int(need),), torch.uint8)
 
     # ------------------------------------------------------------------ optimizer

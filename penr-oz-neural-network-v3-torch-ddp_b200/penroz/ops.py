@@ -4,6 +4,7 @@ torch is only the allocator and stream owner here: every function takes CUDA ten
 and the current stream through ctypes, and returns tensors it allocated. No function falls back to a torch op.
 """
 import math
+import os
 
 import torch
 
@@ -156,8 +157,22 @@ def attn_fwd(qkv, H, want_lse=True, out=None, lse=None):
         out = torch.empty((B, T, C), device=qkv.device, dtype=qkv.dtype)
     if want_lse and lse is None:
         lse = torch.empty((B, H, T), device=qkv.device, dtype=torch.float32)
-    lib().attn_fwd_simt(ptr(qkv), ptr(out), ptr(lse), B, T, H, D, dt(qkv), stream())
+    if _use_tc_attention(qkv, D):
+        lib().attn_fwd_tc(ptr(qkv), ptr(out), ptr(lse), B, T, H, D, stream())
+    else:
+        lib().attn_fwd_simt(ptr(qkv), ptr(out), ptr(lse), B, T, H, D, dt(qkv), stream())
     return out, lse
+
+
+def _use_tc_attention(qkv, D) -> bool:
+    """bf16 + head_dim 64 -> tcgen05 kernels; fp32 models and other head sizes -> exact FP32-pipe kernels."""
+    return qkv.dtype == torch.bfloat16 and D == 64 and os.environ.get("PENROZ_ATTENTION", "tc") != "simt"
+
+
+def attn_bwd_scratch_bytes(B, T, H, D, dtype) -> int:
+    if dtype == torch.bfloat16 and D == 64:
+        return max(lib().attn_bwd_tc_scratch_bytes(B, T, H, D), lib().attn_bwd_scratch_bytes(B, T, H))
+    return lib().attn_bwd_scratch_bytes(B, T, H)
 
 
 def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None):
@@ -166,9 +181,13 @@ def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None):
     if dqkv is None:
         dqkv = torch.empty_like(qkv)
     if scratch is None:
-        scratch = torch.empty(lib().attn_bwd_scratch_bytes(B, T, H), device=qkv.device, dtype=torch.uint8)
-    lib().attn_bwd_simt(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, dt(qkv), ptr(scratch),
-                        scratch.numel(), stream())
+        scratch = torch.empty(attn_bwd_scratch_bytes(B, T, H, D, qkv.dtype), device=qkv.device, dtype=torch.uint8)
+    if _use_tc_attention(qkv, D):
+        lib().attn_bwd_tc(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, ptr(scratch),
+                          scratch.numel(), stream())
+    else:
+        lib().attn_bwd_simt(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, dt(qkv), ptr(scratch),
+                            scratch.numel(), stream())
     return dqkv
 
 

@@ -200,8 +200,9 @@ def test_gelu_and_colsum_and_cast(dev, tanh):
 # ------------------------------------------------------------------ attention (exact path)
 @pytest.mark.parametrize("B,T,H,D,dtype", [(2, 64, 4, 32, torch.float32), (2, 200, 3, 64, torch.float32),
                                             (1, 1024, 2, 64, torch.bfloat16), (2, 96, 2, 128, torch.float32)])
-def test_attention_simt(dev, B, T, H, D, dtype):
+def test_attention_simt(dev, B, T, H, D, dtype, monkeypatch):
     from penroz import ops
+    monkeypatch.setenv("PENROZ_ATTENTION", "simt")   # the exact FP32-pipe kernels, also for bf16 storage
     torch.manual_seed(T)
     C = H * D
     qkv = (torch.randn(B, T, 3 * C, device=dev)).to(dtype)
@@ -221,6 +222,30 @@ def test_attention_simt(dev, B, T, H, D, dtype):
     ref_d = torch.cat([t.grad.transpose(1, 2).reshape(B, T, C) for t in (q, k, v)], dim=2)
     btol = 2e-5 if dtype == torch.float32 else 1.5e-2
     assert rel_err(dqkv, ref_d) < btol
+
+
+@pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 256, 3), (1, 200, 2), (2, 1024, 4), (1, 1000, 2)])
+def test_attention_tensor_core(dev, B, T, H, monkeypatch):
+    """tcgen05 forward/backward (bf16, head_dim 64) against SDPA evaluated in fp32 on the same bf16 inputs.
+    Tolerance: P, dS and the outputs are rounded to bf16 inside the kernel -> a few bf16 ulps (2^-8) of the scale."""
+    from penroz import ops
+    torch.manual_seed(T * 7 + H)
+    D, C = 64, H * 64
+    qkv = torch.randn(B, T, 3 * C, device=dev).bfloat16()
+    q, k, v = [t.view(B, T, H, D).transpose(1, 2).float().requires_grad_(True) for t in qkv.split(C, dim=2)]
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    out, lse = ops.attn_fwd(qkv, H)
+    assert rel_err(out, ref.transpose(1, 2).reshape(B, T, C)) < 1e-2
+    monkeypatch.setenv("PENROZ_ATTENTION", "simt")
+    out_s, lse_s = ops.attn_fwd(qkv, H)
+    monkeypatch.delenv("PENROZ_ATTENTION")
+    assert (lse - lse_s).abs().max().item() < 5e-3
+    dout = torch.randn(B, T, C, device=dev).bfloat16()
+    ref.backward(dout.float().view(B, T, H, D).transpose(1, 2))
+    dqkv = ops.attn_bwd(qkv, out, dout, lse, H)
+    ref_d = torch.cat([t.grad.transpose(1, 2).reshape(B, T, C) for t in (q, k, v)], dim=2)
+    for name, sl in (("dq", slice(0, C)), ("dk", slice(C, 2 * C)), ("dv", slice(2 * C, 3 * C))):
+        assert rel_err(dqkv[..., sl], ref_d[..., sl]) < 2e-2, name
 
 
 # ------------------------------------------------------------------ cross entropy, AdamW, grad norm
