@@ -45,11 +45,15 @@ struct AttnFwdSmem {
     static constexpr int kK0 = 16384;                // 2 stages x 16 KB
     static constexpr int kV0 = kK0 + 2 * 16384;      // 2 stages x 16 KB
     static constexpr int kP = kV0 + 2 * 16384;       // 32 KB: [2 key blocks][128 rows][64]
-    static constexpr int kBar = kP + 32768;
-    static constexpr int kBytes = kBar + 128 + 1024;  // + alignment slack
+    static constexpr int kBar = kP + 32768;          // 128 B of barriers + tmem slot
+    static constexpr int kMax = kBar + 128;          // [2 parity][2 halves][128 rows] floats: row-max exchange
+    static constexpr int kSum = kMax + 2048;         // [2 halves][128 rows] floats: final row-sum exchange
+    static constexpr int kBytes = kSum + 1024 + 1024;  // + alignment slack
 };
 
-__global__ void __launch_bounds__(160, 2)
+__device__ __forceinline__ void softmax_pair_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__global__ void __launch_bounds__(320, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __restrict__ out,
                    float* __restrict__ lse, int Tn, int H, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
@@ -61,6 +65,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
     const uint32_t q_full = bar, kv_full0 = bar + 8, kv_empty0 = bar + 24, s_full = bar + 40, p_ready = bar + 48,
                    o_full = bar + 56;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + AttnFwdSmem::kBar + 64);
+    float* mx_s = reinterpret_cast<float*>(smem + AttnFwdSmem::kMax);
+    float* sum_s = reinterpret_cast<float*>(smem + AttnFwdSmem::kSum);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_qt = (Tn + AT_BM - 1) / AT_BM;
@@ -70,13 +76,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
     const int row0 = b * Tn + qt * AT_BM;            // first row of this query tile in the [B*T, 3C] matrix
     const int n_kv = qt + 1;
 
-    if (threadIdx.x == 128) {
+    if (threadIdx.x == 256) {
         tma_prefetch_desc(&tmQKV);
         mbar_init(q_full, 1);
         mbar_init(kv_full0, 1); mbar_init(kv_full0 + 8, 1);
         mbar_init(kv_empty0, 1); mbar_init(kv_empty0 + 8, 1);
         mbar_init(s_full, 1);
-        mbar_init(p_ready, 4);
+        mbar_init(p_ready, 8);
         mbar_init(o_full, 1);
         mbar_fence_init();
     }
@@ -90,8 +96,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
     const uint32_t tmem = *tmem_slot;
     const uint32_t tS = tmem, tO = tmem + 128;
 
-    if (warp == 4) {
-        if (lane == 0) {
+    if (warp >= 8) {
+        if (warp == 8 && lane == 0) {
             const uint32_t sQ = sbase + AttnFwdSmem::kQ;
             const uint32_t sP = sbase + AttnFwdSmem::kP;
             mbar_expect_tx(q_full, 16384);
@@ -135,26 +141,30 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
         }
         __syncwarp();
     } else {
-        // ------------------------------------------------ softmax / output threads: one query row each
-        const int r = warp * 32 + lane;
+        // ------------------------------------------------ softmax / output threads: 8 warps, two threads per query row.
+        // TMEM lane quarter = warp % 4 (hardware rule); warps 0-3 own key columns 0..63 of every S tile and output
+        // columns 0..31, warps 4-7 the other halves. The pair shares its row maximum through smem each tile; the row
+        // sums stay private until the end.
+        const int qd = warp & 3, half = warp >> 2;
+        const int r = qd * 32 + lane;
         const int i = qt * AT_BM + r;                      // query position inside the sequence
-        const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
-        float o[AT_D];
+        const uint32_t lane_addr = (uint32_t)(qd * 32) << 16;
+        float o[32];
 #pragma unroll
-        for (int d = 0; d < AT_D; ++d) o[d] = 0.f;
+        for (int d = 0; d < 32; ++d) o[d] = 0.f;
         float m = -INFINITY, l = 0.f;
-        uint8_t* sPp = smem + AttnFwdSmem::kP;
+        uint8_t* blk = smem + AttnFwdSmem::kP + half * 16384;   // this half's 64-key block of P
         for (int j = 0; j < n_kv; ++j) {
             mbar_wait(s_full, (uint32_t)(j & 1));
             tc_fence_after();
             const bool diag = (j == qt);
-            const int key0 = j * AT_BN;
-            // pass 1: row maximum
+            const int key0 = j * AT_BN + half * 64;
+            // pass 1: maximum over this thread's 64 columns, then over the pair
             float mt = -INFINITY;
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < 2; ++c) {
                 uint32_t v[32];
-                tmem_ld_32x32(tS + lane_addr + c * 32, v);
+                tmem_ld_32x32(tS + lane_addr + half * 64 + c * 32, v);
                 tmem_ld_wait();
 #pragma unroll
                 for (int k = 0; k < 32; ++k) {
@@ -163,14 +173,18 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                     mt = fmaxf(mt, sv);
                 }
             }
+            float* mx = mx_s + (j & 1) * 256;
+            mx[half * 128 + r] = mt;
+            softmax_pair_sync();
+            mt = fmaxf(mt, mx[(half ^ 1) * 128 + r]);
             const float mn = fmaxf(m, mt * scale_log2e);   // scale > 0: max commutes with the scaling
             const float corr = exp2f(m - mn);              // m = -inf on the first tile -> 0
             float ls = 0.f;
-            // pass 2: p = 2^(s*scale*log2e - mn), row sum, P -> smem (bf16, swizzled K-major)
+            // pass 2: p = 2^(s*scale*log2e - mn), partial row sum, P -> smem (bf16, swizzled K-major)
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < 2; ++c) {
                 uint32_t v[32];
-                tmem_ld_32x32(tS + lane_addr + c * 32, v);
+                tmem_ld_32x32(tS + lane_addr + half * 64 + c * 32, v);
                 tmem_ld_wait();
                 uint32_t packed[16];
 #pragma unroll
@@ -185,14 +199,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                     ls += back.x + back.y;
                     packed[k >> 1] = *reinterpret_cast<uint32_t*>(&hb);
                 }
-                // 32 keys = 4 chunks of 16 B inside key block (c >> 1), columns (c & 1) * 32 ..
-                uint8_t* blk = sPp + (c >> 1) * 16384;
 #pragma unroll
-                for (int q4 = 0; q4 < 4; ++q4) {
-                    const int col = (c & 1) * 32 + q4 * 8;
-                    *reinterpret_cast<uint4*>(blk + sw128_off(r, col)) =
+                for (int q4 = 0; q4 < 4; ++q4)
+                    *reinterpret_cast<uint4*>(blk + sw128_off(r, c * 32 + q4 * 8)) =
                         make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
-                }
             }
             tc_fence_before();
             fence_async_smem();
@@ -202,21 +212,23 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
             m = mn;
             mbar_wait(o_full, (uint32_t)(j & 1));
             tc_fence_after();
-#pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
+            {
                 uint32_t v[32];
-                tmem_ld_32x32(tO + lane_addr + c * 32, v);
+                tmem_ld_32x32(tO + lane_addr + half * 32, v);
                 tmem_ld_wait();
 #pragma unroll
-                for (int k = 0; k < 32; ++k) o[c * 32 + k] = o[c * 32 + k] * corr + __uint_as_float(v[k]);
+                for (int k = 0; k < 32; ++k) o[k] = o[k] * corr + __uint_as_float(v[k]);
             }
             tc_fence_before();
         }
+        sum_s[half * 128 + r] = l;
+        softmax_pair_sync();
+        l += sum_s[(half ^ 1) * 128 + r];
         if (i < Tn) {
             const float inv = 1.f / l;
-            __nv_bfloat16* op = out + ((size_t)(b * Tn + i)) * C + h * AT_D;
+            __nv_bfloat16* op = out + ((size_t)(b * Tn + i)) * C + h * AT_D + half * 32;
 #pragma unroll
-            for (int d = 0; d < AT_D; d += 8) {
+            for (int d = 0; d < 32; d += 8) {
                 uint4 w;
                 w.x = pack_bf16x2(o[d] * inv, o[d + 1] * inv);
                 w.y = pack_bf16x2(o[d + 2] * inv, o[d + 3] * inv);
@@ -224,7 +236,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                 w.w = pack_bf16x2(o[d + 6] * inv, o[d + 7] * inv);
                 *reinterpret_cast<uint4*>(op + d) = w;
             }
-            if (lse) lse[((size_t)b * H + h) * Tn + i] = (m + log2f(l)) * 0.69314718055994530942f;
+            if (lse && half == 0) lse[((size_t)b * H + h) * Tn + i] = (m + log2f(l)) * 0.69314718055994530942f;
         }
     }
     tc_fence_before();
@@ -272,7 +284,7 @@ struct AttnBwdSmem {
     static constexpr int kBytes = kBar + 128 + 1024;
 };
 
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
                    __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2e) {
@@ -293,14 +305,14 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const int C = H * AT_D;
     const int n_it = n_qt - jt;                        // query tiles jt .. n_qt-1
 
-    if (threadIdx.x == 128) {
+    if (threadIdx.x == 256) {
         tma_prefetch_desc(&tmQKV);
         tma_prefetch_desc(&tmDO);
         mbar_init(kv_full, 1);
         mbar_init(qg_full0, 1); mbar_init(qg_full0 + 8, 1);
         mbar_init(qg_empty0, 1); mbar_init(qg_empty0 + 8, 1);
         mbar_init(sdp_full, 1);
-        mbar_init(pds_ready, 4);
+        mbar_init(pds_ready, 8);
         mbar_init(dq_full, 1);
         mbar_fence_init();
     }
@@ -314,7 +326,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const uint32_t tmem = *tmem_slot;
     const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 320, tDQ = tmem + 384;
 
-    if (warp == 5) {
+    if (warp == 9) {
         // ------------------------------------------------ TMA producer
         if (lane == 0) {
             mbar_expect_tx(kv_full, 32768);
@@ -330,7 +342,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             }
         }
         __syncwarp();
-    } else if (warp == 4) {
+    } else if (warp == 8) {
         // ------------------------------------------------ MMA issuer
         if (lane == 0) {
             const uint32_t sK = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV;
@@ -372,9 +384,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         }
         __syncwarp();
     } else {
-        // ------------------------------------------------ softmax-gradient threads: one query row (TMEM lane) each
-        const int r = warp * 32 + lane;
-        const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+        // ------------------------------------------------ softmax-gradient threads: 8 warps, two threads per query row.
+        // TMEM lane quarter = warp % 4 (hardware rule); warps 0-3 take key columns 0..63 (key block 0), warps 4-7
+        // columns 64..127 (key block 1). lse and delta are precomputed, so the two halves never talk to each other.
+        const int qd = warp & 3, half = warp >> 2;
+        const int r = qd * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(qd * 32) << 16;
         uint8_t* sPp = smem + AttnBwdSmem::kP;
         uint8_t* sDSp = smem + AttnBwdSmem::kDS;
         const float log2e = 1.44269504088896340736f;
@@ -390,7 +405,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             mbar_wait(sdp_full, (uint32_t)(it & 1));
             tc_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 2 * half; c < 2 * half + 2; ++c) {
                 uint32_t sv[32], dv[32];
                 tmem_ld_32x32(tS + lane_addr + c * 32, sv);
                 tmem_ld_32x32(tDP + lane_addr + c * 32, dv);
@@ -424,7 +439,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             tc_fence_after();
             float* dq = dq_accum + ((size_t)(b * Tn) + (row_ok ? i : 0)) * C + h * AT_D;
 #pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
+            for (int c = half; c < half + 1; ++c) {
                 uint32_t v[32];
                 __syncwarp();
                 tmem_ld_32x32(tDQ + lane_addr + c * 32, v);
@@ -451,7 +466,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             const uint32_t taddr = which == 0 ? tDV : tDK;
             __nv_bfloat16* dst = which == 0 ? gv : gk;
 #pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
+            for (int c = half; c < half + 1; ++c) {
                 uint32_t v[32];
                 __syncwarp();
                 tmem_ld_32x32(taddr + lane_addr + c * 32, v);
@@ -526,7 +541,7 @@ extern "C" int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B,
     }
     dim3 grid((T + AT_BM - 1) / AT_BM, H, B);
     const float scale_log2e = (1.0f / sqrtf((float)D)) * 1.44269504088896340736f;
-    attn_fwd_tc_kernel<<<grid, 160, AttnFwdSmem::kBytes, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, scale_log2e);
+    attn_fwd_tc_kernel<<<grid, 320, AttnFwdSmem::kBytes, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, scale_log2e);
     count_launch();
     return check_launch("attn_fwd_tc");
 }
@@ -569,7 +584,7 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     attn_bwd_delta_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
-    attn_bwd_tc_kernel<<<grid, 192, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
+    attn_bwd_tc_kernel<<<grid, 320, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
     size_t n4 = rows * C / 4;
     size_t g = (n4 + 255) / 256;
     size_t cap = (size_t)num_sms() * 16;

@@ -56,13 +56,189 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
            (1ull << 46) | (2ull << 61);
 }
 
+
+// ------------------------------------------------------------------ epilogue helpers (one warp, one 32x32 chunk)
+// stg: per-warp staging tile, 32 rows x 33 floats. "own row" access = stg[lane*33 + i]; "coalesced" access walks
+// rows with 4 (bf16, 8 values) or 8 (fp32, 4 values) lanes per row.
+template <typename T>
+__device__ __forceinline__ void stage_load_rows(float* stg, const T* g, long long ld, int lane, int row0, int col0, int M);
+template <>
+__device__ __forceinline__ void stage_load_rows<float>(float* stg, const float* g, long long ld, int lane, int row0,
+                                                       int col0, int M) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int r = 4 * k + (lane >> 3), c = (lane & 7) * 4;
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row0 + r < M) w = *reinterpret_cast<const float4*>(g + (long long)(row0 + r) * ld + col0 + c);
+        float* d = stg + r * 33 + c;
+        d[0] = w.x; d[1] = w.y; d[2] = w.z; d[3] = w.w;
+    }
+}
+template <>
+__device__ __forceinline__ void stage_load_rows<__nv_bfloat16>(float* stg, const __nv_bfloat16* g, long long ld,
+                                                               int lane, int row0, int col0, int M) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int r = 8 * k + (lane >> 2), c = (lane & 3) * 8;
+        uint4 w = make_uint4(0u, 0u, 0u, 0u);
+        if (row0 + r < M) w = *reinterpret_cast<const uint4*>(g + (long long)(row0 + r) * ld + col0 + c);
+        const float2 a = unpack_bf16x2(w.x), b = unpack_bf16x2(w.y), cc = unpack_bf16x2(w.z), d2 = unpack_bf16x2(w.w);
+        float* d = stg + r * 33 + c;
+        d[0] = a.x; d[1] = a.y; d[2] = b.x; d[3] = b.y; d[4] = cc.x; d[5] = cc.y; d[6] = d2.x; d[7] = d2.y;
+    }
+}
+__device__ __forceinline__ void stage_store_rows_bf16(const float* stg, __nv_bfloat16* g, long long ld, int lane,
+                                                      int row0, int col0, int M) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int r = 8 * k + (lane >> 2), c = (lane & 3) * 8;
+        const float* d = stg + r * 33 + c;
+        uint4 w;
+        w.x = pack_bf16x2(d[0], d[1]); w.y = pack_bf16x2(d[2], d[3]);
+        w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
+        if (row0 + r < M) *reinterpret_cast<uint4*>(g + (long long)(row0 + r) * ld + col0 + c) = w;
+    }
+}
+// mode 0 store, 1 load-add-store, 2 red.add
+__device__ __forceinline__ void stage_store_rows_f32(const float* stg, float* g, long long ld, int lane, int row0,
+                                                     int col0, int M, int mode) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int r = 4 * k + (lane >> 3), c = (lane & 7) * 4;
+        const float* d = stg + r * 33 + c;
+        if (row0 + r < M) {
+            float* o = g + (long long)(row0 + r) * ld + col0 + c;
+            if (mode == 2) {
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o), "f"(d[0]), "f"(d[1]), "f"(d[2]),
+                             "f"(d[3])
+                             : "memory");
+            } else {
+                float4 w = make_float4(d[0], d[1], d[2], d[3]);
+                if (mode == 1) {
+                    const float4 old = *reinterpret_cast<const float4*>(o);
+                    w.x += old.x; w.y += old.y; w.z += old.z; w.w += old.w;
+                }
+                *reinterpret_cast<float4*>(o) = w;
+            }
+        }
+    }
+}
+
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&acc)[32], float* stg, int lane, int row0,
+                                               int col0, bool full) {
+    const int row = row0 + lane;
+    const bool row_ok = row < p.M;
+    float* own = stg + lane * 33;
+    // ---- bias (same 64 B for every lane: broadcast loads)
+    if (EPI != EPI_ACCUM_F32 && EPI != EPI_DGELU && p.bias != nullptr) {
+        if (full && ((col0 & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 w = *reinterpret_cast<const uint4*>(p.bias + col0 + 8 * j);
+                const float2 b0 = unpack_bf16x2(w.x), b1 = unpack_bf16x2(w.y), b2 = unpack_bf16x2(w.z), b3 = unpack_bf16x2(w.w);
+                acc[8 * j + 0] += b0.x; acc[8 * j + 1] += b0.y; acc[8 * j + 2] += b1.x; acc[8 * j + 3] += b1.y;
+                acc[8 * j + 4] += b2.x; acc[8 * j + 5] += b2.y; acc[8 * j + 6] += b3.x; acc[8 * j + 7] += b3.y;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (full || col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
+        }
+    }
+    // vector path needs a full chunk and 16-byte aligned rows in every buffer involved
+    bool fast = full;
+    if (EPI == EPI_BF16 || EPI == EPI_GELU || EPI == EPI_DGELU || EPI == EPI_RESID_BF16) fast = fast && (p.ldo % 8 == 0);
+    if (EPI == EPI_GELU) fast = fast && (p.ldo2 % 8 == 0);
+    if (EPI == EPI_DGELU || EPI == EPI_RESID_BF16) fast = fast && (p.ldaux % 8 == 0);
+    if (EPI == EPI_RESID_F32 || EPI == EPI_F32 || EPI == EPI_ACCUM_F32) fast = fast && (p.ldo % 4 == 0);
+    if (EPI == EPI_RESID_F32) fast = fast && (p.ldaux % 4 == 0);
+
+    if (fast) {
+        float aux[32];
+        if (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16) {
+            if (EPI == EPI_RESID_F32) stage_load_rows<float>(stg, reinterpret_cast<const float*>(p.aux), p.ldaux, lane, row0, col0, p.M);
+            else stage_load_rows<__nv_bfloat16>(stg, reinterpret_cast<const __nv_bfloat16*>(p.aux), p.ldaux, lane, row0, col0, p.M);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) aux[i] = own[i];
+            __syncwarp();
+        }
+        if (EPI == EPI_GELU) {
+            // pre-activation first, then the activation, through the same staging tile
+#pragma unroll
+            for (int i = 0; i < 32; ++i) own[i] = acc[i];
+            __syncwarp();
+            stage_store_rows_bf16(stg, reinterpret_cast<__nv_bfloat16*>(p.out), p.ldo, lane, row0, col0, p.M);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float pre = bf16_round(acc[i]);
+                own[i] = p.gelu_tanh ? gelu_tanh_fast(pre) : gelu_erf_fast(pre);
+            }
+            __syncwarp();
+            stage_store_rows_bf16(stg, reinterpret_cast<__nv_bfloat16*>(p.out2), p.ldo2, lane, row0, col0, p.M);
+            __syncwarp();
+            return;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            float r = acc[i];
+            if (EPI == EPI_DGELU) r = bf16_round(acc[i]) * (p.gelu_tanh ? gelu_tanh_grad_fast(aux[i]) : gelu_erf_grad_fast(aux[i]));
+            if (EPI == EPI_RESID_F32 || EPI == EPI_RESID_BF16) r = aux[i] + bf16_round(acc[i]);
+            own[i] = r;
+        }
+        __syncwarp();
+        if (EPI == EPI_BF16 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16)
+            stage_store_rows_bf16(stg, reinterpret_cast<__nv_bfloat16*>(p.out), p.ldo, lane, row0, col0, p.M);
+        else
+            stage_store_rows_f32(stg, reinterpret_cast<float*>(p.out), p.ldo, lane, row0, col0, p.M,
+                                 (EPI == EPI_ACCUM_F32) ? ((p.splits > 1) ? 2 : (p.beta ? 1 : 0)) : 0);
+        __syncwarp();
+        return;
+    }
+    // ---- edge chunks / unaligned leading dimensions: one thread per row, element by element
+    if (!row_ok) return;
+    if (EPI == EPI_BF16 || EPI == EPI_GELU || EPI == EPI_DGELU || EPI == EPI_RESID_BF16) {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * p.ldo + col0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            if (col0 + i >= p.N) continue;   // fully unrolled + predicated: acc[] stays in registers
+            float r = acc[i];
+            if (EPI == EPI_DGELU) {
+                const float hv = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.aux)[(long long)row * p.ldaux + col0 + i]);
+                r = bf16_round(r) * (p.gelu_tanh ? gelu_tanh_grad_fast(hv) : gelu_erf_grad_fast(hv));
+            }
+            if (EPI == EPI_RESID_BF16)
+                r = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.aux)[(long long)row * p.ldaux + col0 + i]) + bf16_round(r);
+            o[i] = __float2bfloat16_rn(r);
+            if (EPI == EPI_GELU) {
+                const float pre = bf16_round(acc[i]);
+                reinterpret_cast<__nv_bfloat16*>(p.out2)[(long long)row * p.ldo2 + col0 + i] =
+                    __float2bfloat16_rn(p.gelu_tanh ? gelu_tanh_fast(pre) : gelu_erf_fast(pre));
+            }
+        }
+    } else {
+        float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            if (col0 + i >= p.N) continue;
+            if (EPI == EPI_RESID_F32) o[i] = reinterpret_cast<const float*>(p.aux)[(long long)row * p.ldaux + col0 + i] + bf16_round(acc[i]);
+            else if (EPI == EPI_F32) o[i] = acc[i];
+            else if (p.splits > 1) atomicAdd(o + i, acc[i]);
+            else o[i] = p.beta ? o[i] + acc[i] : acc[i];
+        }
+    }
+}
+
 template <int BN> struct GemmCfg {
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kStages = (BN == 256) ? 4 : 6;
     static constexpr int kTmemCols = 2 * BN;  // 512 or 256: power of two >= 32
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int kStagingBytes = 8 * 32 * 33 * 4;  // epilogue staging tiles, one per epilogue warp
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kStagingBytes;
 };
 
 template <int BN, int EPI>
@@ -193,9 +369,13 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else if (warp >= 4) {
         // ------------------------------------------------------------ epilogue: 8 warps. TMEM lane quarter = warp % 4
         // (hardware rule), column half = (warp - 4) / 4: two warps per SM sub-partition hide each other's latency.
+        // A thread owns one accumulator row (that is how tcgen05.ld hands TMEM out), but global memory wants a warp to
+        // touch whole rows: every 32x32 chunk goes through a per-warp smem staging tile (row stride 33 floats, conflict
+        // free both ways) so that global loads of aux and global stores are row-contiguous 16-byte accesses.
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
         constexpr int kChunks = BN / 64;   // 32-column chunks per warp
+        float* stg = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256) + (warp - 4) * (32 * 33);
         int as = 0;
         uint32_t aph = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -204,170 +384,21 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int n0 = (tile % p.tiles_n) * BN;
             mbar_wait(tfull_bar(as), aph);
             tc_fence_after();
-            const int row = m0 + q * 32 + lane;
-            const bool row_ok = row < p.M;
+            const int row0 = m0 + q * 32;      // first of this warp's 32 rows
 #pragma unroll 1
             for (int cc = 0; cc < kChunks; ++cc) {
                 const int c = half * kChunks + cc;
                 uint32_t v[32];
-                __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the predicated stores below
+                __syncwarp();  // tcgen05.ld is .sync.aligned
                 tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
                 tmem_ld_wait();
                 const int col0 = n0 + c * 32;
-                if (col0 >= p.N) continue;  // warp-uniform
+                if (col0 >= p.N || row0 >= p.M) continue;  // warp-uniform
                 const bool full = (col0 + 32 <= p.N);
                 float acc[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
-                if (EPI != EPI_ACCUM_F32 && EPI != EPI_DGELU && p.bias != nullptr) {
-                    if (full && ((col0 & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0)) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {   // same 16 B for every lane: one broadcast request
-                            const uint4 w = *reinterpret_cast<const uint4*>(p.bias + col0 + 8 * j);
-                            const float2 b0 = unpack_bf16x2(w.x), b1 = unpack_bf16x2(w.y), b2 = unpack_bf16x2(w.z), b3 = unpack_bf16x2(w.w);
-                            acc[8 * j + 0] += b0.x; acc[8 * j + 1] += b0.y; acc[8 * j + 2] += b1.x; acc[8 * j + 3] += b1.y;
-                            acc[8 * j + 4] += b2.x; acc[8 * j + 5] += b2.y; acc[8 * j + 6] += b3.x; acc[8 * j + 7] += b3.y;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (full || col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
-                    }
-                }
-                if (!row_ok) {
-                    // rows past M (TMA zero-filled): nothing to store
-                } else if (EPI == EPI_BF16 || EPI == EPI_GELU || EPI == EPI_DGELU) {
-                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * p.ldo + col0;
-                    __nv_bfloat16* o2 = nullptr;
-                    if (EPI == EPI_GELU) o2 = reinterpret_cast<__nv_bfloat16*>(p.out2) + (long long)row * p.ldo2 + col0;
-                    float r[32], r2[32];
-                    if (EPI == EPI_DGELU) {
-                        const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (long long)row * p.ldaux + col0;
-                        float hv[32];
-                        if (full && (p.ldaux % 8 == 0)) {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const uint4 w = reinterpret_cast<const uint4*>(h)[j];
-                                const float2 h0 = unpack_bf16x2(w.x), h1 = unpack_bf16x2(w.y), h2 = unpack_bf16x2(w.z), h3 = unpack_bf16x2(w.w);
-                                hv[8 * j + 0] = h0.x; hv[8 * j + 1] = h0.y; hv[8 * j + 2] = h1.x; hv[8 * j + 3] = h1.y;
-                                hv[8 * j + 4] = h2.x; hv[8 * j + 5] = h2.y; hv[8 * j + 6] = h3.x; hv[8 * j + 7] = h3.y;
-                            }
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) hv[i] = (full || col0 + i < p.N) ? __bfloat162float(h[i]) : 0.f;
-                        }
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const float g = p.gelu_tanh ? gelu_tanh_grad_fast(hv[i]) : gelu_erf_grad_fast(hv[i]);
-                            r[i] = bf16_round(acc[i]) * g;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            r[i] = acc[i];
-                            if (EPI == EPI_GELU) {
-                                const float pre = bf16_round(acc[i]);
-                                r2[i] = p.gelu_tanh ? gelu_tanh_fast(pre) : gelu_erf_fast(pre);
-                            }
-                        }
-                    }
-                    if (full && (p.ldo % 8 == 0)) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            uint4 w;
-                            w.x = pack_bf16x2(r[8 * j + 0], r[8 * j + 1]);
-                            w.y = pack_bf16x2(r[8 * j + 2], r[8 * j + 3]);
-                            w.z = pack_bf16x2(r[8 * j + 4], r[8 * j + 5]);
-                            w.w = pack_bf16x2(r[8 * j + 6], r[8 * j + 7]);
-                            reinterpret_cast<uint4*>(o)[j] = w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (col0 + i < p.N) o[i] = __float2bfloat16_rn(r[i]);
-                    }
-                    if (EPI == EPI_GELU) {
-                        if (full && (p.ldo2 % 8 == 0)) {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                uint4 w;
-                                w.x = pack_bf16x2(r2[8 * j + 0], r2[8 * j + 1]);
-                                w.y = pack_bf16x2(r2[8 * j + 2], r2[8 * j + 3]);
-                                w.z = pack_bf16x2(r2[8 * j + 4], r2[8 * j + 5]);
-                                w.w = pack_bf16x2(r2[8 * j + 6], r2[8 * j + 7]);
-                                reinterpret_cast<uint4*>(o2)[j] = w;
-                            }
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (col0 + i < p.N) o2[i] = __float2bfloat16_rn(r2[i]);
-                        }
-                    }
-                } else if (EPI == EPI_RESID_F32 || EPI == EPI_F32) {
-                    float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
-                    const float* x = (EPI == EPI_RESID_F32)
-                                         ? reinterpret_cast<const float*>(p.aux) + (long long)row * p.ldaux + col0
-                                         : nullptr;
-                    if (full && (p.ldo % 4 == 0) && (EPI == EPI_F32 || p.ldaux % 4 == 0)) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (EPI == EPI_RESID_F32) rr = reinterpret_cast<const float4*>(x)[j];
-                            float4 w;
-                            if (EPI == EPI_RESID_F32) {
-                                w.x = rr.x + bf16_round(acc[4 * j + 0]);
-                                w.y = rr.y + bf16_round(acc[4 * j + 1]);
-                                w.z = rr.z + bf16_round(acc[4 * j + 2]);
-                                w.w = rr.w + bf16_round(acc[4 * j + 3]);
-                            } else {
-                                w = make_float4(acc[4 * j + 0], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
-                            }
-                            reinterpret_cast<float4*>(o)[j] = w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (col0 + i < p.N)
-                                o[i] = (EPI == EPI_RESID_F32) ? x[i] + bf16_round(acc[i]) : acc[i];
-                    }
-                } else if (EPI == EPI_RESID_BF16) {
-                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)row * p.ldo + col0;
-                    const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (long long)row * p.ldaux + col0;
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (full || col0 + i < p.N)
-                            o[i] = __float2bfloat16_rn(__bfloat162float(x[i]) + bf16_round(acc[i]));
-                } else {  // EPI_ACCUM_F32
-                    float* o = reinterpret_cast<float*>(p.out) + (long long)row * p.ldo + col0;
-                    if (p.splits > 1) {
-                        if (full && (p.ldo % 4 == 0)) {
-#pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + 4 * j),
-                                             "f"(acc[4 * j + 0]), "f"(acc[4 * j + 1]), "f"(acc[4 * j + 2]),
-                                             "f"(acc[4 * j + 3])
-                                             : "memory");
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (col0 + i < p.N) atomicAdd(o + i, acc[i]);
-                        }
-                    } else if (full && (p.ldo % 4 == 0)) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            float4 w = make_float4(acc[4 * j + 0], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
-                            if (p.beta) {
-                                float4 old = reinterpret_cast<const float4*>(o)[j];
-                                w.x += old.x; w.y += old.y; w.z += old.z; w.w += old.w;
-                            }
-                            reinterpret_cast<float4*>(o)[j] = w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (col0 + i < p.N) o[i] = p.beta ? o[i] + acc[i] : acc[i];
-                    }
-                }
+                epilogue_chunk<EPI>(p, acc, stg, lane, row0, col0, full);
             }
             tc_fence_before();
             __syncwarp();

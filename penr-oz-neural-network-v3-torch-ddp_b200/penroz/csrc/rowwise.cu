@@ -228,6 +228,89 @@ layernorm_bwd_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, const 
     }
 }
 
+// Two-kernel form used for wide launches (enough rows to fill the GPU): (1) a row kernel that only produces dx
+// (few registers -> high occupancy -> HBM-bound), (2) a column kernel that re-reads dy, x and the written gradient
+// and accumulates dgamma/dbeta/dcol for 4 columns per thread over a slice of the rows.
+template <typename TX, typename TW, typename TG, int J>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_rows_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, const TW* __restrict__ gamma,
+                          const float* __restrict__ mean, const float* __restrict__ rstd, const TX* __restrict__ add,
+                          TX* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, int rows, int C) {
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const TG* dyr = dy + (size_t)row * C;
+    const TX* xr = x + (size_t)row * C;
+    const float mu = mean[row], rs = rstd[row];
+    float4 dyg[J], xh[J];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int i = (lane + 32 * j) * 4;
+        if (i < C) {
+            const float4 d = load4(dyr + i), xv = load4(xr + i), g = load4(gamma + i);
+            xh[j] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+            dyg[j] = make_float4(d.x * g.x, d.y * g.y, d.z * g.z, d.w * g.w);
+            s1 += (dyg[j].x + dyg[j].y) + (dyg[j].z + dyg[j].w);
+            s2 += (dyg[j].x * xh[j].x + dyg[j].y * xh[j].y) + (dyg[j].z * xh[j].z + dyg[j].w * xh[j].w);
+        }
+    }
+    s1 = warp_sum(s1) / (float)C;
+    s2 = warp_sum(s2) / (float)C;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int i = (lane + 32 * j) * 4;
+        if (i < C) {
+            float4 r;
+            r.x = rs * (dyg[j].x - s1 - xh[j].x * s2);
+            r.y = rs * (dyg[j].y - s1 - xh[j].y * s2);
+            r.z = rs * (dyg[j].z - s1 - xh[j].z * s2);
+            r.w = rs * (dyg[j].w - s1 - xh[j].w * s2);
+            if (add) {
+                const float4 a = load4(add + (size_t)row * C + i);
+                r.x += a.x; r.y += a.y; r.z += a.z; r.w += a.w;
+            }
+            store4(dx + (size_t)row * C + i, r);
+            if (dx_bf16) store4(dx_bf16 + (size_t)row * C + i, r);
+        }
+    }
+}
+
+// scratch[blockIdx.y][q][c]: q = 0 sum dy*xhat, 1 sum dy, 2 sum of the written gradient (bf16 copy when present)
+template <typename TX, typename TG>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_cols_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, const float* __restrict__ mean,
+                          const float* __restrict__ rstd, const TX* __restrict__ dx,
+                          const __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ scratch, int rows, int C,
+                          int want_dcol) {
+    __shared__ float4 sm[3][8][32];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int col = (blockIdx.x * 32 + tx) * 4;
+    const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
+    const int r0 = blockIdx.y * rows_per, r1 = min(rows, r0 + rows_per);
+    float4 ag = make_float4(0.f, 0.f, 0.f, 0.f), ab = ag, ac = ag;
+    if (col < C) {
+        for (int r = r0 + ty; r < r1; r += 8) {
+            const float mu = mean[r], rs = rstd[r];
+            const float4 d = load4(dy + (size_t)r * C + col), xv = load4(x + (size_t)r * C + col);
+            ag.x += d.x * (xv.x - mu) * rs; ag.y += d.y * (xv.y - mu) * rs;
+            ag.z += d.z * (xv.z - mu) * rs; ag.w += d.w * (xv.w - mu) * rs;
+            ab.x += d.x; ab.y += d.y; ab.z += d.z; ab.w += d.w;
+            if (want_dcol) {
+                const float4 g = dx_bf16 ? load4(dx_bf16 + (size_t)r * C + col) : load4(dx + (size_t)r * C + col);
+                ac.x += g.x; ac.y += g.y; ac.z += g.z; ac.w += g.w;
+            }
+        }
+    }
+    sm[0][ty][tx] = ag; sm[1][ty][tx] = ab; sm[2][ty][tx] = ac;
+    __syncthreads();
+    if (ty < 3 && col < C) {
+        float4 s = sm[ty][0][tx];
+        for (int k = 1; k < 8; ++k) { const float4 v = sm[ty][k][tx]; s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+        *reinterpret_cast<float4*>(scratch + ((size_t)blockIdx.y * 3 + ty) * C + col) = s;
+    }
+}
+
 // out_q[c] += sum_blocks scratch[b][q][c]   (fixed order: deterministic)
 __global__ void layernorm_bwd_reduce_kernel(const float* __restrict__ scratch, int nblocks, int C,
                                             float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -417,9 +500,33 @@ int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const f
     PENROZ_REQUIRE(C <= 2048, "layernorm_bwd: C=%d exceeds the supported 2048", C);
     PENROZ_REQUIRE(scratch != nullptr, "layernorm_bwd: scratch is required");
     const int J = (C + 127) / 128;
-    const int grid = ln_bwd_grid(rows);
-    const bool fuse_dcol = dcol != nullptr && J <= 8;
+    int grid = ln_bwd_grid(rows);
+    bool fuse_dcol = dcol != nullptr && J <= 8;
     int rc = -1;
+    const bool wide = rows >= 4096;   // enough rows to fill the GPU with the one-row-per-warp kernel
+    if (wide) {
+        const int rgrid = (rows + 7) / 8;
+#define LN_ROWS_J(TX, TW, TG, j) layernorm_bwd_rows_kernel<TX, TW, TG, j><<<rgrid, 256, 0, st>>>((const TG*)dy, (const TX*)x, (const TW*)gamma, mean, rstd, (const TX*)add, (TX*)dx, (__nv_bfloat16*)dx_bf16, rows, C)
+#define LN_ROWS(TX, TW, TG)                                                      \
+        if (J <= 1) LN_ROWS_J(TX, TW, TG, 1); else if (J <= 2) LN_ROWS_J(TX, TW, TG, 2); \
+        else if (J <= 4) LN_ROWS_J(TX, TW, TG, 4); else if (J <= 6) LN_ROWS_J(TX, TW, TG, 6); \
+        else if (J <= 8) LN_ROWS_J(TX, TW, TG, 8); else if (J <= 13) LN_ROWS_J(TX, TW, TG, 13); \
+        else LN_ROWS_J(TX, TW, TG, 16)
+        grid = ln_bwd_grid(rows);        // number of row slices == partial-sum slots in scratch
+        dim3 cg((C + 127) / 128, grid);
+        if (x_dtype == F32 && w_dtype == F32 && dy_dtype == BF16) {
+            LN_ROWS(float, float, __nv_bfloat16);
+            layernorm_bwd_cols_kernel<float, __nv_bfloat16><<<cg, 256, 0, st>>>((const __nv_bfloat16*)dy, (const float*)x, mean, rstd, (const float*)dx, (const __nv_bfloat16*)dx_bf16, scratch, rows, C, dcol != nullptr);
+        } else if (x_dtype == F32 && w_dtype == F32 && dy_dtype == F32) {
+            LN_ROWS(float, float, float);
+            layernorm_bwd_cols_kernel<float, float><<<cg, 256, 0, st>>>((const float*)dy, (const float*)x, mean, rstd, (const float*)dx, (const __nv_bfloat16*)dx_bf16, scratch, rows, C, dcol != nullptr);
+        } else { set_error("layernorm_bwd: unsupported dtypes x=%d w=%d dy=%d", x_dtype, w_dtype, dy_dtype); return PENROZ_ERR_ARG; }
+#undef LN_ROWS
+#undef LN_ROWS_J
+        fuse_dcol = dcol != nullptr;
+        rc = 0;
+        count_launch(1);
+    } else {
 #define LN_BWD(TX, TW, TG)                                                                                              \
     rc = fuse_dcol ? dispatch_ln_bwd_j<true, TX, TW, TG>(J, dy, x, gamma, mean, rstd, add, dx, dx_bf16, scratch, rows, C, grid, st) \
                    : dispatch_ln_bwd_j<false, TX, TW, TG>(J, dy, x, gamma, mean, rstd, add, dx, dx_bf16, scratch, rows, C, grid, st)
@@ -427,6 +534,7 @@ int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const f
     else if (x_dtype == F32 && w_dtype == F32 && dy_dtype == F32) { LN_BWD(float, float, float); }
     else { set_error("layernorm_bwd: unsupported dtypes x=%d w=%d dy=%d", x_dtype, w_dtype, dy_dtype); return PENROZ_ERR_ARG; }
 #undef LN_BWD
+    }
     if (rc != 0) { set_error("layernorm_bwd: no kernel for C=%d", C); return PENROZ_ERR_ARG; }
     dim3 rg((C + 255) / 256, fuse_dcol ? 3 : 2);
     layernorm_bwd_reduce_kernel<<<rg, 256, 0, st>>>(scratch, grid, C, dgamma, dbeta, fuse_dcol ? dcol : nullptr);
