@@ -159,18 +159,20 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
             tc_fence_after();
             const bool diag = (j == qt);
             const int key0 = j * AT_BN + half * 64;
-            // pass 1: maximum over this thread's 64 columns, then over the pair
+            // pass 1: maximum over this thread's 64 columns, then over the pair (mask only on the diagonal tile)
             float mt = -INFINITY;
 #pragma unroll 1
             for (int c = 0; c < 2; ++c) {
                 uint32_t v[32];
                 tmem_ld_32x32(tS + lane_addr + half * 64 + c * 32, v);
                 tmem_ld_wait();
+                if (diag) {
 #pragma unroll
-                for (int k = 0; k < 32; ++k) {
-                    float sv = __uint_as_float(v[k]);
-                    if (diag && key0 + c * 32 + k > i) sv = -INFINITY;
-                    mt = fmaxf(mt, sv);
+                    for (int k = 0; k < 32; ++k)
+                        mt = fmaxf(mt, (key0 + c * 32 + k > i) ? -INFINITY : __uint_as_float(v[k]));
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) mt = fmaxf(mt, __uint_as_float(v[k]));
                 }
             }
             float* mx = mx_s + (j & 1) * 256;
@@ -178,7 +180,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
             softmax_pair_sync();
             mt = fmaxf(mt, mx[(half ^ 1) * 128 + r]);
             const float mn = fmaxf(m, mt * scale_log2e);   // scale > 0: max commutes with the scaling
-            const float corr = exp2f(m - mn);              // m = -inf on the first tile -> 0
+            const float corr = ex2_fast(m - mn);           // m = -inf on the first tile -> 0
             float ls = 0.f;
             // pass 2: p = 2^(s*scale*log2e - mn), partial row sum, P -> smem (bf16, swizzled K-major)
 #pragma unroll 1
@@ -189,10 +191,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                 uint32_t packed[16];
 #pragma unroll
                 for (int k = 0; k < 32; k += 2) {
-                    float a = __uint_as_float(v[k]) * scale_log2e - mn;
-                    float bb = __uint_as_float(v[k + 1]) * scale_log2e - mn;
-                    float pa = (diag && key0 + c * 32 + k > i) ? 0.f : exp2f(a);
-                    float pb = (diag && key0 + c * 32 + k + 1 > i) ? 0.f : exp2f(bb);
+                    float pa = ex2_fast(fmaf(__uint_as_float(v[k]), scale_log2e, -mn));
+                    float pb = ex2_fast(fmaf(__uint_as_float(v[k + 1]), scale_log2e, -mn));
+                    if (diag) {
+                        if (key0 + c * 32 + k > i) pa = 0.f;
+                        if (key0 + c * 32 + k + 1 > i) pb = 0.f;
+                    }
                     // the row sum uses the bf16-rounded probabilities the PV product will see
                     __nv_bfloat162 hb = __floats2bfloat162_rn(pa, pb);
                     float2 back = __bfloat1622float2(hb);
@@ -401,6 +405,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             const float L2 = row_ok ? lse[stat] * log2e : 0.f;
             const float dl = row_ok ? delta[stat] : 0.f;
             const bool diag = (it == 0);
+            const bool edge = diag || ((qt + 1) * AT_BM > Tn);
             const int key0 = jt * AT_BN;
             mbar_wait(sdp_full, (uint32_t)(it & 1));
             tc_fence_after();
@@ -413,10 +418,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 uint32_t pp[16], dd[16];
 #pragma unroll
                 for (int k = 0; k < 32; k += 2) {
-                    float p0 = exp2f(__uint_as_float(sv[k]) * scale_log2e - L2);
-                    float p1 = exp2f(__uint_as_float(sv[k + 1]) * scale_log2e - L2);
-                    if (!row_ok || (diag && key0 + c * 32 + k > i)) p0 = 0.f;
-                    if (!row_ok || (diag && key0 + c * 32 + k + 1 > i)) p1 = 0.f;
+                    float p0 = ex2_fast(fmaf(__uint_as_float(sv[k]), scale_log2e, -L2));
+                    float p1 = ex2_fast(fmaf(__uint_as_float(sv[k + 1]), scale_log2e, -L2));
+                    if (edge) {   // diagonal tile or a tile with rows past the sequence end: warp-uniform flag
+                        if (!row_ok || (diag && key0 + c * 32 + k > i)) p0 = 0.f;
+                        if (!row_ok || (diag && key0 + c * 32 + k + 1 > i)) p1 = 0.f;
+                    }
                     const float d0 = p0 * (__uint_as_float(dv[k]) - dl) * scale;
                     const float d1 = p1 * (__uint_as_float(dv[k + 1]) - dl) * scale;
                     pp[k >> 1] = pack_bf16x2(p0, p1);

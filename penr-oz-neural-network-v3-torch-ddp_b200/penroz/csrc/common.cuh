@@ -131,9 +131,19 @@ __device__ __forceinline__ float gelu_tanh_grad(float x) {
 // Branch-free variants for the tensor-core epilogues, whose outputs are rounded to bf16 (2^-9 relative): erf by
 // Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7), exp/reciprocal/tanh on the SFU. No branches, so the 32 independent
 // elements a thread holds pipeline instead of serialising on erff's control flow.
-__device__ __forceinline__ float erf_and_gauss_fast(float z, float& gauss) {   // z >= 0 handled by the callers' sign fix
+__device__ __forceinline__ float rcp_fast(float x) {   // MUFU.RCP, no slow-path branch (x is in [1, inf) here)
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float ex2_fast(float x) {   // MUFU.EX2; -inf -> 0, large negative -> 0 (ftz)
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float erf_and_gauss_fast(float z, float& gauss) {
     const float az = fabsf(z);
-    const float t = __frcp_rn(fmaf(0.3275911f, az, 1.f));
+    const float t = rcp_fast(fmaf(0.3275911f, az, 1.f));
     gauss = __expf(-az * az);
     float poly = fmaf(1.061405429f, t, -1.453152027f);
     poly = fmaf(poly, t, 1.421413741f);

@@ -171,22 +171,33 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&acc)
             __syncwarp();
             stage_store_rows_bf16(stg, reinterpret_cast<__nv_bfloat16*>(p.out), p.ldo, lane, row0, col0, p.M);
             __syncwarp();
+            if (p.gelu_tanh) {   // warp-uniform choice outside the element loop: straight-line code per element
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float pre = bf16_round(acc[i]);
-                own[i] = p.gelu_tanh ? gelu_tanh_fast(pre) : gelu_erf_fast(pre);
+                for (int i = 0; i < 32; ++i) own[i] = gelu_tanh_fast(bf16_round(acc[i]));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) own[i] = gelu_erf_fast(bf16_round(acc[i]));
             }
             __syncwarp();
             stage_store_rows_bf16(stg, reinterpret_cast<__nv_bfloat16*>(p.out2), p.ldo2, lane, row0, col0, p.M);
             __syncwarp();
             return;
         }
+        if (EPI == EPI_DGELU) {
+            if (p.gelu_tanh) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-            float r = acc[i];
-            if (EPI == EPI_DGELU) r = bf16_round(acc[i]) * (p.gelu_tanh ? gelu_tanh_grad_fast(aux[i]) : gelu_erf_grad_fast(aux[i]));
-            if (EPI == EPI_RESID_F32 || EPI == EPI_RESID_BF16) r = aux[i] + bf16_round(acc[i]);
-            own[i] = r;
+                for (int i = 0; i < 32; ++i) own[i] = bf16_round(acc[i]) * gelu_tanh_grad_fast(aux[i]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) own[i] = bf16_round(acc[i]) * gelu_erf_grad_fast(aux[i]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                float r = acc[i];
+                if (EPI == EPI_RESID_F32 || EPI == EPI_RESID_BF16) r = aux[i] + bf16_round(acc[i]);
+                own[i] = r;
+            }
         }
         __syncwarp();
         if (EPI == EPI_BF16 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16)
