@@ -159,6 +159,33 @@ def run_reference_arm(args):
     print(json.dumps(line))
 
 
+def decode_bench(torch, nnm, device):
+    """BASELINE config 4: greedy KV-cache generation through the public generate_tokens() API (prefill of a 512-token
+    prompt + 64 new tokens), batch 1 and 64, bf16 (HF-import style) and fp32 parameters. tokens/s = B * new / wall."""
+    out = {}
+    V = CFG["V"]
+    for tag, dtype in (("bf16", torch.bfloat16), ("f32", torch.float32)):
+        model = build_model(f"dec_{tag}")
+        if dtype != torch.float32:
+            model.to(dtype=dtype)
+        model.to("cuda")
+        for B in (1, 64):
+            gen = torch.Generator().manual_seed(7)
+            prompt = torch.randint(0, V, (B, 512), generator=gen).tolist()
+            model.generate_tokens([p[:16] for p in prompt], 1024, 4, temperature=0.0)     # warm-up
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            toks = model.generate_tokens(prompt, 1024, 64, temperature=0.0)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            assert len(toks) == 512 + 64
+            out[f"{tag}_b{B}"] = {"tokens_per_s": B * 64 / dt, "seconds": dt}
+        del model
+        torch.cuda.empty_cache()
+    out["workload"] = "GPT-2 124M greedy generate_tokens: 512-token prompt + 64 new tokens (prefill included), context 1024"
+    return out
+
+
 # ---------------------------------------------------------------------------------------------------- our arm
 class KernelTimer:
     """CUDA-event pairs around every launch of the C-ABI families that matter, for the roofline object."""
@@ -297,7 +324,7 @@ def run_ours(args):
             torch.cuda.synchronize()
             s_all, e_all = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s_all.record()
-            step(0)
+            step(0)                       # every rank runs this step (it contains the gradient all-reduce)
             e_all.record()
             fam = kt.summary()
         step_ms = s_all.elapsed_time(e_all)
@@ -310,6 +337,8 @@ def run_ours(args):
                     "frac": achieved / peak, "traffic": None, "peak_source": f"{which} (sustained: kernel timed inside a long step)",
                     "share_of_step": d["ms"] / step_ms, "launches_per_step": d["launches"],
                     "families_ms": {k: round(v["ms"], 3) for k, v in fam.items()}, "instrumented_step_ms": step_ms}
+    else:
+        step(0)
     barrier()
 
     # ---------------- e2e: the public API, host shards in, loss out, every step
@@ -341,6 +370,14 @@ def run_ours(args):
                "api": "NeuralNetworkModel.train_model (uint16 shards on the host -> int64 batch H2D -> fused step -> cost.item())",
                "steps": n}
 
+    decode = None
+    if rank == 0 and world == 1:
+        del model, eng
+        torch.cuda.empty_cache()
+        try:
+            decode = decode_bench(torch, nnm, device)
+        except Exception as exc:  # the train metric is the headline; report, do not lose the line
+            decode = {"error": repr(exc)}
     if rank == 0:
         cpu_rate, cores, sample, _ = cpu_reference_step_rate(1, 1) if world == 1 else (None, None, None, None)
         ft = f_tok(cfg["L"], cfg["C"], V, T)
@@ -357,7 +394,8 @@ def run_ours(args):
                 "mfu_vs_2.25PF": value * ft / (world * 2.25e15),
                 "mfu_vs_measured_sustained": value * ft / (world * peaks["bf16_tflops_sustained"] * 1e12),
                 "flops_per_token": ft, "final_loss": final_loss,
-                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+                "decode": decode}
         if cpu_rate is not None:
             line["cpu_baseline"] = {"value": cpu_rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         print(json.dumps(line))

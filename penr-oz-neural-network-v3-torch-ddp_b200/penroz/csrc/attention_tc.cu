@@ -41,9 +41,11 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int col) {
 
 // ---------------------------------------------------------------------------------------------- forward
 struct AttnFwdSmem {
+    // sized so that TWO CTAs fit in one SM's 227 KB (one CTA's softmax overlaps the other's MMAs): K is single
+    // buffered (its only reader, the S MMA, retires long before the next K is needed), V double buffered
     static constexpr int kQ = 0;                     // 16 KB
-    static constexpr int kK0 = 16384;                // 2 stages x 16 KB
-    static constexpr int kV0 = kK0 + 2 * 16384;      // 2 stages x 16 KB
+    static constexpr int kK0 = 16384;                // 16 KB
+    static constexpr int kV0 = kK0 + 16384;          // 2 stages x 16 KB
     static constexpr int kP = kV0 + 2 * 16384;       // 32 KB: [2 key blocks][128 rows][64]
     static constexpr int kBar = kP + 32768;          // 128 B of barriers + tmem slot
     static constexpr int kMax = kBar + 128;          // [2 parity][2 halves][128 rows] floats: row-max exchange
@@ -62,9 +64,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
     uint8_t* smem = smem_raw + pad;
     const uint32_t sbase = raw + pad;
     const uint32_t bar = sbase + AttnFwdSmem::kBar;
-    const uint32_t q_full = bar, kv_full0 = bar + 8, kv_empty0 = bar + 24, s_full = bar + 40, p_ready = bar + 48,
-                   o_full = bar + 56;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + AttnFwdSmem::kBar + 64);
+    const uint32_t q_full = bar, v_full0 = bar + 8, v_empty0 = bar + 24, s_full = bar + 40, p_ready = bar + 48,
+                   o_full = bar + 56, k_full = bar + 64, k_empty = bar + 72;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + AttnFwdSmem::kBar + 96);
     float* mx_s = reinterpret_cast<float*>(smem + AttnFwdSmem::kMax);
     float* sum_s = reinterpret_cast<float*>(smem + AttnFwdSmem::kSum);
 
@@ -79,8 +81,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
     if (threadIdx.x == 256) {
         tma_prefetch_desc(&tmQKV);
         mbar_init(q_full, 1);
-        mbar_init(kv_full0, 1); mbar_init(kv_full0 + 8, 1);
-        mbar_init(kv_empty0, 1); mbar_init(kv_empty0 + 8, 1);
+        mbar_init(v_full0, 1); mbar_init(v_full0 + 8, 1);
+        mbar_init(v_empty0, 1); mbar_init(v_empty0 + 8, 1);
+        mbar_init(k_full, 1); mbar_init(k_empty, 1);
         mbar_init(s_full, 1);
         mbar_init(p_ready, 8);
         mbar_init(o_full, 1);
@@ -102,41 +105,51 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
             const uint32_t sP = sbase + AttnFwdSmem::kP;
             mbar_expect_tx(q_full, 16384);
             tma_load_2d(sQ, &tmQKV, q_full, h * AT_D, row0);
-            mbar_expect_tx(kv_full0, 32768);
-            tma_load_2d(sbase + AttnFwdSmem::kK0, &tmQKV, kv_full0, C + h * AT_D, b * Tn);
-            tma_load_2d(sbase + AttnFwdSmem::kV0, &tmQKV, kv_full0, 2 * C + h * AT_D, b * Tn);
+            const uint32_t sK = sbase + AttnFwdSmem::kK0;
+            mbar_expect_tx(k_full, 16384);
+            tma_load_2d(sK, &tmQKV, k_full, C + h * AT_D, b * Tn);
+            mbar_expect_tx(v_full0, 16384);
+            tma_load_2d(sbase + AttnFwdSmem::kV0, &tmQKV, v_full0, 2 * C + h * AT_D, b * Tn);
             const uint32_t idS = at_idesc(0, 0, AT_BN);
             const uint32_t idO = at_idesc(0, 1, AT_D);
+            constexpr uint32_t kHi = desc_hi(64u);
             mbar_wait(q_full, 0);
             for (int j = 0; j < n_kv; ++j) {
                 const int s = j & 1;
-                const uint32_t sK = sbase + AttnFwdSmem::kK0 + s * 16384;
                 const uint32_t sV = sbase + AttnFwdSmem::kV0 + s * 16384;
-                mbar_wait(kv_full0 + 8 * s, (uint32_t)((j >> 1) & 1));
+                mbar_wait(k_full, (uint32_t)(j & 1));
                 tc_fence_after();
+                {
+                    const uint32_t q_lo = desc_lo(sQ, 1), k_lo = desc_lo(sK, 1);
 #pragma unroll
-                for (int k4 = 0; k4 < AT_D / 16; ++k4)
-                    umma_bf16(tS, at_desc(sQ + k4 * 32, 1, 64), at_desc(sK + k4 * 32, 1, 64), idS, (uint32_t)(k4 != 0));
+                    for (int k4 = 0; k4 < AT_D / 16; ++k4)
+                        umma_bf16(tS, desc_make(q_lo + k4 * 2, kHi), desc_make(k_lo + k4 * 2, kHi), idS, (uint32_t)(k4 != 0));
+                }
                 umma_commit(s_full);
+                umma_commit(k_empty);
                 if (j + 1 < n_kv) {
                     const int s2 = s ^ 1;
-                    if (j >= 1) mbar_wait(kv_empty0 + 8 * s2, (uint32_t)(((j - 1) >> 1) & 1));
-                    mbar_expect_tx(kv_full0 + 8 * s2, 32768);
-                    tma_load_2d(sbase + AttnFwdSmem::kK0 + s2 * 16384, &tmQKV, kv_full0 + 8 * s2, C + h * AT_D,
-                                b * Tn + (j + 1) * AT_BN);
-                    tma_load_2d(sbase + AttnFwdSmem::kV0 + s2 * 16384, &tmQKV, kv_full0 + 8 * s2, 2 * C + h * AT_D,
+                    mbar_wait(k_empty, (uint32_t)(j & 1));          // S_j has consumed K_j: refill the single K buffer
+                    mbar_expect_tx(k_full, 16384);
+                    tma_load_2d(sK, &tmQKV, k_full, C + h * AT_D, b * Tn + (j + 1) * AT_BN);
+                    if (j >= 1) mbar_wait(v_empty0 + 8 * s2, (uint32_t)(((j - 1) >> 1) & 1));
+                    mbar_expect_tx(v_full0 + 8 * s2, 16384);
+                    tma_load_2d(sbase + AttnFwdSmem::kV0 + s2 * 16384, &tmQKV, v_full0 + 8 * s2, 2 * C + h * AT_D,
                                 b * Tn + (j + 1) * AT_BN);
                 }
+                mbar_wait(v_full0 + 8 * s, (uint32_t)((j >> 1) & 1));
                 mbar_wait(p_ready, (uint32_t)(j & 1));
                 tc_fence_after();
                 // O_j = P V_j : A = P K-major (two 64-key blocks 16 KB apart), B = V MN-major (16 keys = 2048 B per step)
+                {
+                    const uint32_t p_lo = desc_lo(sP, 1), v_lo = desc_lo(sV, 512);
 #pragma unroll
-                for (int k8 = 0; k8 < AT_BN / 16; ++k8) {
-                    const uint32_t pa = sP + (k8 >> 2) * 16384 + (k8 & 3) * 32;
-                    umma_bf16(tO, at_desc(pa, 1, 64), at_desc(sV + k8 * 2048, 512, 64), idO, (uint32_t)(k8 != 0));
+                    for (int k8 = 0; k8 < AT_BN / 16; ++k8)
+                        umma_bf16(tO, desc_make(p_lo + (k8 >> 2) * 1024 + (k8 & 3) * 2, kHi), desc_make(v_lo + k8 * 128, kHi), idO,
+                                  (uint32_t)(k8 != 0));
                 }
                 umma_commit(o_full);
-                umma_commit(kv_empty0 + 8 * s);
+                umma_commit(v_empty0 + 8 * s);
             }
         }
         __syncwarp();
@@ -354,6 +367,11 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             const uint32_t id_kk128 = at_idesc(0, 0, 128);   // A K-major, B K-major, N=128  (S, dP)
             const uint32_t id_mm64 = at_idesc(1, 1, 64);     // A MN-major, B MN-major, N=64 (dV, dK)
             const uint32_t id_km64 = at_idesc(0, 1, 64);     // A K-major, B MN-major, N=64  (dQ)
+            constexpr uint32_t kHi = desc_hi(64u);
+            // loop-invariant descriptor words: K/V as K-major B (S, dP), K as MN-major B (dQ),
+            // P/dS as MN-major A (dV, dK; 64-key blocks 16 KB apart) and dS as K-major A (dQ)
+            const uint32_t k_lo = desc_lo(sK, 1), v_lo = desc_lo(sV, 1), km_lo = desc_lo(sK, 512);
+            const uint32_t pm_lo = desc_lo(sP, 1024), dsm_lo = desc_lo(sDS, 1024), dsk_lo = desc_lo(sDS, 1);
             mbar_wait(kv_full, 0);
             for (int it = 0; it < n_it; ++it) {
                 const int s = it & 1;
@@ -361,26 +379,28 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 const uint32_t sG = sbase + AttnBwdSmem::kG0 + s * 16384;
                 mbar_wait(qg_full0 + 8 * s, (uint32_t)((it >> 1) & 1));
                 tc_fence_after();
+                const uint32_t q_lo = desc_lo(sQ, 1), g_lo = desc_lo(sG, 1);
 #pragma unroll
                 for (int k4 = 0; k4 < 4; ++k4)   // S = Q K^T
-                    umma_bf16(tS, at_desc(sQ + k4 * 32, 1, 64), at_desc(sK + k4 * 32, 1, 64), id_kk128, (uint32_t)(k4 != 0));
+                    umma_bf16(tS, desc_make(q_lo + k4 * 2, kHi), desc_make(k_lo + k4 * 2, kHi), id_kk128, (uint32_t)(k4 != 0));
 #pragma unroll
                 for (int k4 = 0; k4 < 4; ++k4)   // dP = dO V^T
-                    umma_bf16(tDP, at_desc(sG + k4 * 32, 1, 64), at_desc(sV + k4 * 32, 1, 64), id_kk128, (uint32_t)(k4 != 0));
+                    umma_bf16(tDP, desc_make(g_lo + k4 * 2, kHi), desc_make(v_lo + k4 * 2, kHi), id_kk128, (uint32_t)(k4 != 0));
                 umma_commit(sdp_full);
                 mbar_wait(pds_ready, (uint32_t)(it & 1));
                 tc_fence_after();
+                const uint32_t qm_lo = desc_lo(sQ, 512), gm_lo = desc_lo(sG, 512);
 #pragma unroll
-                for (int k8 = 0; k8 < 8; ++k8)   // dV += P^T dO   (M = keys, K = queries)
-                    umma_bf16(tDV, at_desc(sP + k8 * 2048, 1024, 64), at_desc(sG + k8 * 2048, 512, 64), id_mm64,
+                for (int k8 = 0; k8 < 8; ++k8)   // dV += P^T dO   (M = keys, K = queries; both operands MN-major)
+                    umma_bf16(tDV, desc_make(pm_lo + k8 * 128, kHi), desc_make(gm_lo + k8 * 128, kHi), id_mm64,
                               (uint32_t)((it | k8) != 0));
 #pragma unroll
                 for (int k8 = 0; k8 < 8; ++k8)   // dK += dS^T Q
-                    umma_bf16(tDK, at_desc(sDS + k8 * 2048, 1024, 64), at_desc(sQ + k8 * 2048, 512, 64), id_mm64,
+                    umma_bf16(tDK, desc_make(dsm_lo + k8 * 128, kHi), desc_make(qm_lo + k8 * 128, kHi), id_mm64,
                               (uint32_t)((it | k8) != 0));
 #pragma unroll
                 for (int k8 = 0; k8 < 8; ++k8)   // dQ_i = dS K   (M = queries, K = keys)
-                    umma_bf16(tDQ, at_desc(sDS + (k8 >> 2) * 16384 + (k8 & 3) * 32, 1, 64), at_desc(sK + k8 * 2048, 512, 64),
+                    umma_bf16(tDQ, desc_make(dsk_lo + (k8 >> 2) * 1024 + (k8 & 3) * 2, kHi), desc_make(km_lo + k8 * 128, kHi),
                               id_km64, (uint32_t)(k8 != 0));
                 umma_commit(dq_full);
                 umma_commit(qg_empty0 + 8 * s);
@@ -397,13 +417,17 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         uint8_t* sPp = smem + AttnBwdSmem::kP;
         uint8_t* sDSp = smem + AttnBwdSmem::kDS;
         const float log2e = 1.44269504088896340736f;
+        const size_t stat0 = ((size_t)b * H + h) * Tn;
+        float lse_next = 0.f, dl_next = 0.f;
+        if (jt * AT_BM + r < Tn) { lse_next = lse[stat0 + jt * AT_BM + r]; dl_next = delta[stat0 + jt * AT_BM + r]; }
         for (int it = 0; it < n_it; ++it) {
             const int qt = jt + it;
             const int i = qt * AT_BM + r;               // query position
             const bool row_ok = i < Tn;
-            const size_t stat = ((size_t)b * H + h) * Tn + (row_ok ? i : 0);
-            const float L2 = row_ok ? lse[stat] * log2e : 0.f;
-            const float dl = row_ok ? delta[stat] : 0.f;
+            const float L2 = lse_next * log2e;          // fetched one iteration ahead: no exposed global latency
+            const float dl = dl_next;
+            if (it + 1 < n_it && i + AT_BM < Tn) { lse_next = lse[stat0 + i + AT_BM]; dl_next = delta[stat0 + i + AT_BM]; }
+            else { lse_next = 0.f; dl_next = 0.f; }
             const bool diag = (it == 0);
             const bool edge = diag || ((qt + 1) * AT_BM > Tn);
             const int key0 = jt * AT_BN;

@@ -124,9 +124,63 @@ __device__ __forceinline__ void stage_store_rows_f32(const float* stg, float* g,
     }
 }
 
+// aux operand of a chunk, fetched one chunk ahead into registers (row-coalesced mapping) and later dropped into the
+// staging tile: fp32 aux uses 8 x 16 B per lane, bf16 aux 4 x 16 B.
+template <int EPI>
+__device__ __forceinline__ void aux_issue(const GemmParams& p, uint4 (&pre)[8], int lane, int row0, int col0) {
+    if (EPI == EPI_RESID_F32) {
+        const float* g = reinterpret_cast<const float*>(p.aux);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int r = 4 * k + (lane >> 3), c = (lane & 7) * 4;
+            pre[k] = make_uint4(0u, 0u, 0u, 0u);
+            if (row0 + r < p.M) pre[k] = *reinterpret_cast<const uint4*>(g + (long long)(row0 + r) * p.ldaux + col0 + c);
+        }
+    } else if (EPI == EPI_DGELU || EPI == EPI_RESID_BF16) {
+        const __nv_bfloat16* g = reinterpret_cast<const __nv_bfloat16*>(p.aux);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int r = 8 * k + (lane >> 2), c = (lane & 3) * 8;
+            pre[k] = make_uint4(0u, 0u, 0u, 0u);
+            if (row0 + r < p.M) pre[k] = *reinterpret_cast<const uint4*>(g + (long long)(row0 + r) * p.ldaux + col0 + c);
+        }
+    }
+}
+template <int EPI>
+__device__ __forceinline__ void aux_deposit(float* stg, const uint4 (&pre)[8], int lane) {
+    if (EPI == EPI_RESID_F32) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int r = 4 * k + (lane >> 3), c = (lane & 7) * 4;
+            float* d = stg + r * 33 + c;
+            d[0] = __uint_as_float(pre[k].x); d[1] = __uint_as_float(pre[k].y);
+            d[2] = __uint_as_float(pre[k].z); d[3] = __uint_as_float(pre[k].w);
+        }
+    } else if (EPI == EPI_DGELU || EPI == EPI_RESID_BF16) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int r = 8 * k + (lane >> 2), c = (lane & 3) * 8;
+            const float2 a = unpack_bf16x2(pre[k].x), b = unpack_bf16x2(pre[k].y), cc = unpack_bf16x2(pre[k].z), d2 = unpack_bf16x2(pre[k].w);
+            float* d = stg + r * 33 + c;
+            d[0] = a.x; d[1] = a.y; d[2] = b.x; d[3] = b.y; d[4] = cc.x; d[5] = cc.y; d[6] = d2.x; d[7] = d2.y;
+        }
+    }
+}
+// can this chunk take the vector path? (full 32 columns and 16-byte aligned rows in every buffer involved)
+template <int EPI>
+__device__ __forceinline__ bool chunk_is_fast(const GemmParams& p, int col0) {
+    bool fast = (col0 + 32 <= p.N);
+    if (EPI == EPI_BF16 || EPI == EPI_GELU || EPI == EPI_DGELU || EPI == EPI_RESID_BF16) fast = fast && (p.ldo % 8 == 0);
+    if (EPI == EPI_GELU) fast = fast && (p.ldo2 % 8 == 0);
+    if (EPI == EPI_DGELU || EPI == EPI_RESID_BF16) fast = fast && (p.ldaux % 8 == 0);
+    if (EPI == EPI_RESID_F32 || EPI == EPI_F32 || EPI == EPI_ACCUM_F32) fast = fast && (p.ldo % 4 == 0);
+    if (EPI == EPI_RESID_F32) fast = fast && (p.ldaux % 4 == 0);
+    return fast;
+}
+
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&acc)[32], float* stg, int lane, int row0,
-                                               int col0, bool full) {
+                                               int col0, bool full, uint4 (&pre)[8], bool pre_valid, int next_col0) {
     const int row = row0 + lane;
     const bool row_ok = row < p.M;
     float* own = stg + lane * 33;
@@ -146,23 +200,20 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&acc)
                 if (full || col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
         }
     }
-    // vector path needs a full chunk and 16-byte aligned rows in every buffer involved
-    bool fast = full;
-    if (EPI == EPI_BF16 || EPI == EPI_GELU || EPI == EPI_DGELU || EPI == EPI_RESID_BF16) fast = fast && (p.ldo % 8 == 0);
-    if (EPI == EPI_GELU) fast = fast && (p.ldo2 % 8 == 0);
-    if (EPI == EPI_DGELU || EPI == EPI_RESID_BF16) fast = fast && (p.ldaux % 8 == 0);
-    if (EPI == EPI_RESID_F32 || EPI == EPI_F32 || EPI == EPI_ACCUM_F32) fast = fast && (p.ldo % 4 == 0);
-    if (EPI == EPI_RESID_F32) fast = fast && (p.ldaux % 4 == 0);
+    const bool fast = chunk_is_fast<EPI>(p, col0);
+    constexpr bool kHasAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16);
 
     if (fast) {
         float aux[32];
-        if (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16) {
-            if (EPI == EPI_RESID_F32) stage_load_rows<float>(stg, reinterpret_cast<const float*>(p.aux), p.ldaux, lane, row0, col0, p.M);
-            else stage_load_rows<__nv_bfloat16>(stg, reinterpret_cast<const __nv_bfloat16*>(p.aux), p.ldaux, lane, row0, col0, p.M);
+        if (kHasAux) {
+            if (!pre_valid) aux_issue<EPI>(p, pre, lane, row0, col0);   // first chunk of a tile whose prefetch was skipped
+            aux_deposit<EPI>(stg, pre, lane);
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 32; ++i) aux[i] = own[i];
             __syncwarp();
+            // next chunk's aux goes in flight now and lands while this chunk is computed and stored
+            if (next_col0 >= 0) aux_issue<EPI>(p, pre, lane, row0, next_col0);
         }
         if (EPI == EPI_GELU) {
             // pre-activation first, then the activation, through the same staging tile
@@ -346,6 +397,7 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // MN-major SW128: 64-wide MN blocks 8192 B apart (LBO), 8-k groups 1024 B apart (SBO). k-step = 16 rows = +2048 B.
         const uint32_t a_lbo = p.a_mn ? 512u : 1u, b_lbo = p.b_mn ? 512u : 1u;
         const uint32_t a_step = p.a_mn ? 2048u : 32u, b_step = p.b_mn ? 2048u : 32u;
+        constexpr uint32_t kDescHi = desc_hi(64u);   // SBO = 1024 B for both majors
         int s = 0, as = 0;
         uint32_t ph = 0, aph = 0;
         for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -361,13 +413,11 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     mbar_wait(full_bar(s), ph);
                     tc_fence_after();
                     const uint32_t sA = smem_base + s * Cfg::kStageBytes;
-                    const uint32_t sB = sA + Cfg::kABytes;
+                    const uint32_t a_lo = desc_lo(sA, a_lbo), b_lo = desc_lo(sA + Cfg::kABytes, b_lbo);
 #pragma unroll
-                    for (int k4 = 0; k4 < BK / UK; ++k4) {
-                        const uint64_t adesc = make_smem_desc(sA + k4 * a_step, a_lbo, 64u);
-                        const uint64_t bdesc = make_smem_desc(sB + k4 * b_step, b_lbo, 64u);
-                        umma_bf16(d_tmem, adesc, bdesc, idesc, (uint32_t)((kb | k4) != 0));
-                    }
+                    for (int k4 = 0; k4 < BK / UK; ++k4)
+                        umma_bf16(d_tmem, desc_make(a_lo + k4 * (a_step >> 4), kDescHi), desc_make(b_lo + k4 * (b_step >> 4), kDescHi),
+                                  idesc, (uint32_t)((kb | k4) != 0));
                     umma_commit(empty_bar(s));               // frees the smem slot once these MMAs retire
                     if (kb == nkb - 1) umma_commit(tfull_bar(as));  // accumulator ready for the epilogue
                 }
@@ -393,9 +443,19 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int tile = u % (p.tiles_m * p.tiles_n);
             const int m0 = (tile / p.tiles_n) * BM;
             const int n0 = (tile % p.tiles_n) * BN;
+            const int row0 = m0 + q * 32;      // first of this warp's 32 rows
+            constexpr bool kHasAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16);
+            uint4 pre[8];
+            bool pre_valid = false;
+            {   // the aux operand does not depend on the accumulator: fetch the first chunk's before waiting for the MMAs
+                const int c0 = n0 + half * kChunks * 32;
+                if (kHasAux && row0 < p.M && c0 < p.N && chunk_is_fast<EPI>(p, c0)) {
+                    aux_issue<EPI>(p, pre, lane, row0, c0);
+                    pre_valid = true;
+                }
+            }
             mbar_wait(tfull_bar(as), aph);
             tc_fence_after();
-            const int row0 = m0 + q * 32;      // first of this warp's 32 rows
 #pragma unroll 1
             for (int cc = 0; cc < kChunks; ++cc) {
                 const int c = half * kChunks + cc;
@@ -409,7 +469,10 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 float acc[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
-                epilogue_chunk<EPI>(p, acc, stg, lane, row0, col0, full);
+                int next_col0 = -1;
+                if (kHasAux && cc + 1 < kChunks && col0 + 32 < p.N && chunk_is_fast<EPI>(p, col0 + 32)) next_col0 = col0 + 32;
+                epilogue_chunk<EPI>(p, acc, stg, lane, row0, col0, full, pre, pre_valid, next_col0);
+                pre_valid = (next_col0 >= 0);
             }
             tc_fence_before();
             __syncwarp();
@@ -423,6 +486,203 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tc_fence_before();
     __syncthreads();
     if (warp == 2) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ------------------------------------------------------------------ CTA-pair kernel (cta_group::2)
+// Output tile 256 x 256 per cluster of two CTAs (same TPC): CTA r owns accumulator rows [128 r, 128 r + 128) in its
+// TMEM and loads only its 128 rows of A and its 128-row half of B per k-block (32 KB instead of 48 KB), so the operand
+// traffic per flop through L2 drops by a third and the smem ring gets 6 stages deep. The even CTA issues every
+// tcgen05.mma.cta_group::2 (M = 256) and owns the full / tmem-empty barriers; completion of MMAs is multicast to both
+// CTAs' empty / tmem-full barriers. Epilogue code is shared with the single-CTA kernel.
+struct GemmCfg2 {
+    static constexpr int BN = 256;
+    static constexpr int kABytes = BM * BK * 2;            // 128 rows of A
+    static constexpr int kBBytes = (BN / 2) * BK * 2;      // this CTA's half of B
+    static constexpr int kStageBytes = kABytes + kBBytes;  // 32 KB
+    static constexpr int kStages = 6;
+    static constexpr int kTmemCols = 2 * BN;
+    static constexpr int kStagingBytes = 8 * 32 * 33 * 4;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kStagingBytes;
+};
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
+gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const GemmParams p) {
+    using Cfg = GemmCfg2;
+    constexpr int BN = Cfg::BN;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    const uint32_t pad = (1024u - (raw_addr & 1023u)) & 1023u;
+    uint8_t* smem = smem_raw + pad;
+    const uint32_t smem_base = raw_addr + pad;
+    const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + 2 + s); };
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = (rank == 0);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < Cfg::kStages; ++s) {
+            mbar_init(full_bar(s), 1);     // the leader's producer arrives (with the pair's byte count)
+            mbar_init(empty_bar(s), 1);    // one multicast commit
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tfull_bar(s), 1);    // one multicast commit
+            mbar_init(tempty_bar(s), 16);  // 8 epilogue warps of each CTA (only the leader's copy is used)
+        }
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        tmem_alloc_pair(smem_u32(tmem_ptr_smem), Cfg::kTmemCols);
+        tmem_relinquish_pair();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const int n_clusters = gridDim.x >> 1;
+    const int cid = blockIdx.x >> 1;
+    const int units = p.tiles_m * p.tiles_n * p.splits;   // tiles_m counts 256-row tiles here
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer (both CTAs)
+        int s = 0;
+        uint32_t ph = 0;
+        for (int u = cid; u < units; u += n_clusters) {
+            const int tile = u % (p.tiles_m * p.tiles_n);
+            const int split = u / (p.tiles_m * p.tiles_n);
+            const int m0 = (tile / p.tiles_n) * (2 * BM) + (int)rank * BM;
+            const int n0 = (tile % p.tiles_n) * BN + (int)rank * (BN / 2);
+            const int kb0 = split * p.kb_per_split;
+            const int nkb = min(p.kb_per_split, p.kb_total - kb0);
+            for (int kb = 0; kb < nkb; ++kb) {
+                if (lane == 0) {
+                    mbar_wait(empty_bar(s), ph ^ 1u);
+                    if (leader) mbar_expect_tx(full_bar(s), 2 * Cfg::kStageBytes);
+                    const uint32_t sA = smem_base + s * Cfg::kStageBytes;
+                    const uint32_t sB = sA + Cfg::kABytes;
+                    const int k0 = (kb0 + kb) * BK;
+                    if (!p.a_mn) {
+                        tma_load_2d_pair(sA, &tmA, full_bar(s), k0, m0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j) tma_load_2d_pair(sA + j * 8192, &tmA, full_bar(s), m0 + 64 * j, k0);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_2d_pair(sB, &tmB, full_bar(s), k0, n0);   // box {64 k, 128 rows}
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 128; ++j) tma_load_2d_pair(sB + j * 8192, &tmB, full_bar(s), n0 + 64 * j, k0);
+                    }
+                }
+                __syncwarp();
+                if (++s == Cfg::kStages) { s = 0; ph ^= 1u; }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer (even CTA only)
+        if (leader) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
+                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+            const uint32_t a_lbo = p.a_mn ? 512u : 1u, b_lbo = p.b_mn ? 512u : 1u;
+            const uint32_t a_step = p.a_mn ? 2048u : 32u, b_step = p.b_mn ? 2048u : 32u;
+            constexpr uint32_t kDescHi = desc_hi(64u);
+            int s = 0, as = 0;
+            uint32_t ph = 0, aph = 0;
+            for (int u = cid; u < units; u += n_clusters) {
+                const int split = u / (p.tiles_m * p.tiles_n);
+                const int kb0 = split * p.kb_per_split;
+                const int nkb = min(p.kb_per_split, p.kb_total - kb0);
+                if (lane == 0) mbar_wait(tempty_bar(as), aph ^ 1u);
+                __syncwarp();
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+                for (int kb = 0; kb < nkb; ++kb) {
+                    if (lane == 0) {
+                        mbar_wait(full_bar(s), ph);
+                        tc_fence_after();
+                        const uint32_t sA = smem_base + s * Cfg::kStageBytes;
+                        const uint32_t a_lo = desc_lo(sA, a_lbo), b_lo = desc_lo(sA + Cfg::kABytes, b_lbo);
+#pragma unroll
+                        for (int k4 = 0; k4 < BK / UK; ++k4)
+                            umma_bf16_pair(d_tmem, desc_make(a_lo + k4 * (a_step >> 4), kDescHi),
+                                           desc_make(b_lo + k4 * (b_step >> 4), kDescHi), idesc, (uint32_t)((kb | k4) != 0));
+                        umma_commit_pair(empty_bar(s));
+                        if (kb == nkb - 1) umma_commit_pair(tfull_bar(as));
+                    }
+                    __syncwarp();
+                    if (++s == Cfg::kStages) { s = 0; ph ^= 1u; }
+                }
+                as ^= 1;
+                if (as == 0) aph ^= 1u;
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------ epilogue (both CTAs, own 128 accumulator rows)
+        const int q = warp & 3;
+        const int half = (warp - 4) >> 2;
+        constexpr int kChunks = BN / 64;
+        float* stg = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256) + (warp - 4) * (32 * 33);
+        int as = 0;
+        uint32_t aph = 0;
+        for (int u = cid; u < units; u += n_clusters) {
+            const int tile = u % (p.tiles_m * p.tiles_n);
+            const int m0 = (tile / p.tiles_n) * (2 * BM) + (int)rank * BM;
+            const int n0 = (tile % p.tiles_n) * BN;
+            const int row0 = m0 + q * 32;
+            constexpr bool kHasAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16);
+            uint4 pre[8];
+            bool pre_valid = false;
+            {
+                const int c0 = n0 + half * kChunks * 32;
+                if (kHasAux && row0 < p.M && c0 < p.N && chunk_is_fast<EPI>(p, c0)) {
+                    aux_issue<EPI>(p, pre, lane, row0, c0);
+                    pre_valid = true;
+                }
+            }
+            mbar_wait(tfull_bar(as), aph);
+            tc_fence_after();
+#pragma unroll 1
+            for (int cc = 0; cc < kChunks; ++cc) {
+                const int c = half * kChunks + cc;
+                uint32_t v[32];
+                __syncwarp();
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                tmem_ld_wait();
+                const int col0 = n0 + c * 32;
+                if (col0 >= p.N || row0 >= p.M) continue;
+                const bool full = (col0 + 32 <= p.N);
+                float acc[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
+                int next_col0 = -1;
+                if (kHasAux && cc + 1 < kChunks && col0 + 32 < p.N && chunk_is_fast<EPI>(p, col0 + 32)) next_col0 = col0 + 32;
+                epilogue_chunk<EPI>(p, acc, stg, lane, row0, col0, full, pre, pre_valid, next_col0);
+                pre_valid = (next_col0 >= 0);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_on_leader(tempty_bar(as));
+            as ^= 1;
+            if (as == 0) aph ^= 1u;
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();   // the peer may still be reading this CTA's smem (B halves) or signalling its barriers
+    if (warp == 2) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
 }
 
 // ------------------------------------------------------------------ host side
@@ -479,6 +739,35 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     return check_launch("gemm_bf16_tc");
 }
 
+template <int EPI>
+static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
+    auto kern = gemm_bf16_tc2_kernel<EPI>;
+    static std::atomic<int> configured{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!((configured.load() >> dev) & 1)) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg2::kSmemBytes);
+        if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+        configured.fetch_or(1 << dev);
+    }
+    kern<<<grid, 384, GemmCfg2::kSmemBytes, st>>>(tmA, tmB, p);
+    count_launch();
+    return check_launch("gemm_bf16_tc2");
+}
+static int dispatch_epi2(int epi, const CUtensorMap& a, const CUtensorMap& b, const GemmParams& p, int grid, cudaStream_t st) {
+    switch (epi) {
+        case EPI_BF16: return launch_gemm2<EPI_BF16>(a, b, p, grid, st);
+        case EPI_GELU: return launch_gemm2<EPI_GELU>(a, b, p, grid, st);
+        case EPI_RESID_F32: return launch_gemm2<EPI_RESID_F32>(a, b, p, grid, st);
+        case EPI_RESID_BF16: return launch_gemm2<EPI_RESID_BF16>(a, b, p, grid, st);
+        case EPI_ACCUM_F32: return launch_gemm2<EPI_ACCUM_F32>(a, b, p, grid, st);
+        case EPI_DGELU: return launch_gemm2<EPI_DGELU>(a, b, p, grid, st);
+        case EPI_F32: return launch_gemm2<EPI_F32>(a, b, p, grid, st);
+    }
+    set_error("gemm_bf16: unknown epilogue %d", epi);
+    return PENROZ_ERR_ARG;
+}
+
 template <int BN>
 static int dispatch_epi(int epi, const CUtensorMap& a, const CUtensorMap& b, const GemmParams& p, int grid, cudaStream_t st) {
     switch (epi) {
@@ -525,16 +814,23 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     const int tiles_m = (M + BM - 1) / BM;
     // wide tiles when they still give every SM work; otherwise the 128-wide tile (more CTAs in flight)
     int bn = 256;
-    if (N <= 128 || (long long)tiles_m * ((N + 255) / 256) < sms) bn = 128;
+    if (N <= 128) bn = 128;
+    // few output tiles: narrower tiles put more CTAs to work — except for the weight-gradient form, where split-K
+    // supplies the parallelism and the wide tile moves 25 % fewer operand bytes through L2 per flop
+    else if (epilogue != EPI_ACCUM_F32 && (long long)tiles_m * ((N + 255) / 256) < sms) bn = 128;
     if (flags & 4) bn = 128;
     if (flags & 8) bn = 256;
-    p.tiles_m = tiles_m;
+    // CTA pairs (256 x 256 tiles, cta_group::2) whenever the problem has at least one full pair tile; flags bit 4 forces
+    // the single-CTA kernel (used by the tests to cover both)
+    const bool pair = (bn == 256) && (M >= 256) && !(flags & 16) && (sms >= 2);
+    p.tiles_m = pair ? (M + 2 * BM - 1) / (2 * BM) : tiles_m;
     p.tiles_n = (N + bn - 1) / bn;
     p.kb_total = (K + BK - 1) / BK;
     p.splits = 1;
+    const int workers = pair ? sms / 2 : sms;
     if (epilogue == EPI_ACCUM_F32) {
         const int tiles = p.tiles_m * p.tiles_n;
-        if (tiles < sms) p.splits = max(1, min(p.kb_total, sms / tiles));
+        if (tiles < workers) p.splits = max(1, min(p.kb_total, workers / tiles));
         // red.add accumulates into `out`: with beta == 0 the caller must have zeroed it
         if (p.splits > 1 && !p.beta) {
             cudaError_t e = cudaMemset2DAsync(out, (size_t)ldo * 4, 0, (size_t)N * 4, (size_t)M, st);
@@ -549,10 +845,14 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     if (!p.a_mn) rc = encode_bf16_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, 64, BM);
     else         rc = encode_bf16_2d(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, 64);
     if (rc) return rc;
-    if (!p.b_mn) rc = encode_bf16_2d(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, (uint32_t)bn);
+    if (!p.b_mn) rc = encode_bf16_2d(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, (uint32_t)(pair ? bn / 2 : bn));
     else         rc = encode_bf16_2d(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, 64);
     if (rc) return rc;
 
+    if (pair) {
+        const int units2 = p.tiles_m * p.tiles_n * p.splits;
+        return dispatch_epi2(epilogue, tmA, tmB, p, 2 * min(units2, workers), st);
+    }
     const int units = p.tiles_m * p.tiles_n * p.splits;
     const int grid = min(units, sms);
     if (bn == 256) return dispatch_epi<256>(epilogue, tmA, tmB, p, grid, st);

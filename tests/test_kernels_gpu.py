@@ -29,7 +29,9 @@ def rel_err(a, b):
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 768), (300, 200, 136), (1024, 2304, 768),
                                     (77, 50257, 768), (4096, 768, 3072)])
 @pytest.mark.parametrize("al,bl", [(0, 0), (0, 1), (1, 1), (1, 0)])
-def test_gemm_bf16_layouts(dev, M, N, K, al, bl):
+@pytest.mark.parametrize("single_cta", [0, 16])
+def test_gemm_bf16_layouts(dev, M, N, K, al, bl, single_cta):
+    """single_cta = 16 forces the one-CTA kernel; 0 lets shapes with M, N >= 256 take the CTA-pair (cta_group::2) kernel."""
     from penroz import ops
     if N == 50257 and bl == 1:
         pytest.skip("MN-major operand needs ld % 8 == 0")
@@ -41,11 +43,11 @@ def test_gemm_bf16_layouts(dev, M, N, K, al, bl):
     ref = A.float() @ B.float().t()
     a_in = A if al == 0 else A.t().contiguous()
     b_in = B if bl == 0 else B.t().contiguous()
-    out = ops.gemm(a_in, b_in, a_layout=al, b_layout=bl, epilogue=ops.EPI_F32)
+    out = ops.gemm(a_in, b_in, a_layout=al, b_layout=bl, epilogue=ops.EPI_F32, flags_extra=single_cta)
     torch.cuda.synchronize()
     # fp32 accumulation of exact bf16 products: only summation-order noise
     assert rel_err(out, ref) < 2e-5, f"fp32-out rel err {rel_err(out, ref)}"
-    out_b = ops.gemm(a_in, b_in, a_layout=al, b_layout=bl, epilogue=ops.EPI_STORE)
+    out_b = ops.gemm(a_in, b_in, a_layout=al, b_layout=bl, epilogue=ops.EPI_STORE, flags_extra=single_cta)
     assert torch.equal(out_b, out.bfloat16()) or rel_err(out_b, ref) < 4e-3
 
 
