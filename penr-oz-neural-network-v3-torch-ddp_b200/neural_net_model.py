@@ -559,10 +559,7 @@ class NeuralNetworkModel(nn.Module):
                 speed = window / secs
                 cost_value = cost.item()
                 if epoch % max(1, epochs // 100) == 0:  # at most ~100 progress points
-                    with torch.no_grad():
-                        ratios = [None if (w is None or pw is None) else
-                                  ((w - pw).data.std() / (w.data.std() + 1e-8)).item()
-                                  for pw, w in zip(before, self._weights)]
+                    ratios = self._weight_update_ratios(before)
                     self.progress.append({"dt": dt.now().isoformat(), "epoch": epoch + 1, "durationInSecs": secs,
                                           "speedPerSec": speed, "cost": cost_value, "weight_upd_ratio": ratios})
                 log.info(f"Model {self.model_id}: Training Epoch {epoch + 1}, Cost: {cost_value:.4f}, "
@@ -579,6 +576,20 @@ class NeuralNetworkModel(nn.Module):
             self.serialize()
 
     # ------------------------------------------------------------------ diagnostics (rank 0)
+    @torch.no_grad()
+    def _weight_update_ratios(self, before: list) -> list:
+        """std(w_new - w_old) / (std(w_new) + 1e-8) per 2-D weight, None elsewhere — the reference's arithmetic
+        (neural_net_model.py:696-699) with ONE device->host read for the whole list instead of one sync per weight."""
+        now = self._weights
+        picked = [i for i, (pw, w) in enumerate(zip(before, now)) if w is not None and pw is not None]
+        out = [None] * len(now)
+        if picked:
+            vals = torch.stack([(now[i] - before[i]).data.std() / (now[i].data.std() + 1e-8) for i in picked])
+            for i, v in zip(picked, vals.tolist()):
+                out[i] = v
+        return out
+
+
     @staticmethod
     def _density_histogram(t: Tensor):
         """torch.histogram(density=True) as ([left bin edges], [densities]); bf16 is widened first."""

@@ -262,18 +262,28 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
 }
 
 // ---------------------------------------------------------------------------------------------- backward
-// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (one warp per (row, head))
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]: 8 lanes per (row, head), 16-byte loads, 3-step shuffle reduce
 __global__ void attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
                                       float* __restrict__ delta, int rows, int Tn, int H) {
-    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (gw >= rows * H) return;
-    const int row = gw / H, h = gw % H;
-    const size_t off = (size_t)row * H * AT_D + h * AT_D + lane * 2;
-    const float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(o + off));
-    const float2 g = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(dout + off));
-    const float s = warp_sum(a.x * g.x + a.y * g.y);
-    if (lane == 0) delta[((size_t)(row / Tn) * H + h) * Tn + (row % Tn)] = s;
+    const long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3;   // (row, head) index
+    const int sub = threadIdx.x & 7;
+    float s = 0.f;
+    const bool ok = g < (long long)rows * H;
+    if (ok) {
+        const size_t off = (size_t)g * AT_D + sub * 8;            // [rows, H*64] is contiguous in (row, head)
+        const uint4 a = *reinterpret_cast<const uint4*>(o + off);
+        const uint4 b = *reinterpret_cast<const uint4*>(dout + off);
+        const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+        const float2 b0 = unpack_bf16x2(b.x), b1 = unpack_bf16x2(b.y), b2 = unpack_bf16x2(b.z), b3 = unpack_bf16x2(b.w);
+        s = (a0.x * b0.x + a0.y * b0.y) + (a1.x * b1.x + a1.y * b1.y) + (a2.x * b2.x + a2.y * b2.y) + (a3.x * b3.x + a3.y * b3.y);
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (ok && sub == 0) {
+        const int row = (int)(g / H), h = (int)(g % H);
+        delta[((size_t)(row / Tn) * H + h) * Tn + (row % Tn)] = s;
+    }
 }
 
 // dq_accum (fp32 [rows, C]) -> bf16 into the q third of dqkv [rows, 3C]
@@ -611,8 +621,8 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     }
     cudaError_t e = cudaMemsetAsync(dq_acc, 0, rows * C * sizeof(float), st);
     if (e != cudaSuccess) { set_error("attn_bwd_tc: memset: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
-    const long long warps = (long long)rows * H;
-    attn_bwd_delta_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
+    const long long pairs = (long long)rows * H;
+    attn_bwd_delta_kernel<<<(unsigned)((pairs * 8 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
     attn_bwd_tc_kernel<<<grid, 320, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);

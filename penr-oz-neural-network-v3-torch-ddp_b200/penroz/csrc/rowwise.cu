@@ -361,29 +361,52 @@ __global__ void gelu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ 
 }
 
 // ------------------------------------------------------------------ column sums (bias gradients)
-// part[y][n] = sum over this block's row slice of X[m,n]; 32 x 8 threads, 4 columns per thread.
+// part[y][n] = sum over this block's row slice of X[m,n]; 32 x 8 threads, one 16-byte vector of columns per thread
+// (4 fp32 or 8 bf16), four rows in flight per thread.
 template <typename T>
-__global__ void colsum_partial_kernel(const T* __restrict__ X, long long ld, int M, int N, float* __restrict__ part) {
-    __shared__ float4 sm[8][32];
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const T* __restrict__ X, long long ld, int M, int N, float* __restrict__ part) {
+    constexpr int VN = Vec16<T>::N;
+    __shared__ float sm[8][32][VN + 1];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int col = (blockIdx.x * 32 + tx) * 4;
+    const int col = (blockIdx.x * 32 + tx) * VN;
     const int rows_per = (M + gridDim.y - 1) / gridDim.y;
     const int r0 = blockIdx.y * rows_per, r1 = min(M, r0 + rows_per);
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (col + 3 < N) {
-        for (int r = r0 + ty; r < r1; r += 8) {
-            float4 v = load4(X + (size_t)r * ld + col);
-            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    float s[VN];
+#pragma unroll
+    for (int k = 0; k < VN; ++k) s[k] = 0.f;
+    const bool vec_ok = (col + VN <= N) && (ld % VN == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+    if (vec_ok) {
+        int r = r0 + ty;
+        for (; r + 24 < r1; r += 32) {
+            Vec16<T> v0, v1, v2, v3;
+            v0.load(X + (size_t)r * ld + col);
+            v1.load(X + (size_t)(r + 8) * ld + col);
+            v2.load(X + (size_t)(r + 16) * ld + col);
+            v3.load(X + (size_t)(r + 24) * ld + col);
+#pragma unroll
+            for (int k = 0; k < VN; ++k) s[k] += (v0.get(k) + v1.get(k)) + (v2.get(k) + v3.get(k));
+        }
+        for (; r < r1; r += 8) {
+            Vec16<T> v;
+            v.load(X + (size_t)r * ld + col);
+#pragma unroll
+            for (int k = 0; k < VN; ++k) s[k] += v.get(k);
         }
     } else if (col < N) {
         for (int r = r0 + ty; r < r1; r += 8)
-            for (int k = 0; k < 4 && col + k < N; ++k) (&s.x)[k] += to_f32(X[(size_t)r * ld + col + k]);
+            for (int k = 0; k < VN && col + k < N; ++k) s[k] += to_f32(X[(size_t)r * ld + col + k]);
     }
-    sm[ty][tx] = s;
+#pragma unroll
+    for (int k = 0; k < VN; ++k) sm[ty][tx][k] = s[k];
     __syncthreads();
     if (ty == 0 && col < N) {
-        for (int k = 1; k < 8; ++k) { float4 v = sm[k][tx]; s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
-        for (int k = 0; k < 4 && col + k < N; ++k) part[(size_t)blockIdx.y * N + col + k] = (&s.x)[k];
+        for (int k = 0; k < VN && col + k < N; ++k) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) t += sm[w][tx][k];
+            part[(size_t)blockIdx.y * N + col + k] = t;
+        }
     }
 }
 __global__ void colsum_reduce_kernel(const float* __restrict__ part, int nparts, int N, float* __restrict__ out,
@@ -545,9 +568,9 @@ int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const f
         // wide rows: column sums of the written gradient as a separate pass (re-uses the same scratch)
         const void* src = dx_bf16 ? dx_bf16 : dx;
         const int parts = 32;
-        dim3 g((C + 127) / 128, parts);
+        dim3 g((C + 255) / 256, parts), g4((C + 127) / 128, parts);
         if (dx_bf16) colsum_partial_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)src, C, rows, C, scratch);
-        else colsum_partial_kernel<float><<<g, 256, 0, st>>>((const float*)src, C, rows, C, scratch);
+        else colsum_partial_kernel<float><<<g4, 256, 0, st>>>((const float*)src, C, rows, C, scratch);
         colsum_reduce_kernel<<<(C + 255) / 256, 256, 0, st>>>(scratch, parts, C, dcol, 1);
         count_launch(2);
         return check_launch("layernorm_bwd/colsum");
@@ -596,12 +619,11 @@ extern "C" int penroz_colsum(const void* X, long long ld, int M, int N, float* o
                              void* scratch, size_t scratch_bytes, void* stream) {
     PENROZ_REQUIRE(M > 0 && N > 0, "colsum: bad shape");
     PENROZ_REQUIRE(scratch && scratch_bytes >= penroz_colsum_scratch_bytes(M, N), "colsum: scratch too small");
-    PENROZ_REQUIRE(ld % 4 == 0, "colsum: ld must be a multiple of 4");
     cudaStream_t st = (cudaStream_t)stream;
     const int parts = 32;
-    dim3 g((N + 127) / 128, parts);
-    if (dtype == F32) colsum_partial_kernel<float><<<g, 256, 0, st>>>((const float*)X, ld, M, N, (float*)scratch);
-    else if (dtype == BF16) colsum_partial_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)X, ld, M, N, (float*)scratch);
+    dim3 g4((N + 127) / 128, parts), g8((N + 255) / 256, parts);
+    if (dtype == F32) colsum_partial_kernel<float><<<g4, 256, 0, st>>>((const float*)X, ld, M, N, (float*)scratch);
+    else if (dtype == BF16) colsum_partial_kernel<__nv_bfloat16><<<g8, 256, 0, st>>>((const __nv_bfloat16*)X, ld, M, N, (float*)scratch);
     else { set_error("colsum: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
     colsum_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>((const float*)scratch, parts, N, out, accumulate);
     count_launch(2);
@@ -658,7 +680,6 @@ extern "C" int penroz_colsum_static(const void* X, long long ld, int M, int N, f
                                     void* stream) {
     PENROZ_REQUIRE(M > 0 && N > 0, "colsum_static: bad shape M=%d N=%d", M, N);
     PENROZ_REQUIRE(X != nullptr && out != nullptr, "colsum_static: null argument");
-    PENROZ_REQUIRE(ld % 4 == 0, "colsum_static: ld must be a multiple of 4");
     if (N > kStaticColsumMaxCols) {
         set_error("colsum_static: N=%d exceeds the built-in scratch (at most %d columns); use penroz_colsum with "
                   "caller-provided scratch for wider matrices", N, kStaticColsumMaxCols);
@@ -668,11 +689,11 @@ extern "C" int penroz_colsum_static(const void* X, long long ld, int M, int N, f
     int rc = static_colsum_scratch(&scratch);
     if (rc != PENROZ_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    dim3 g((N + 127) / 128, kStaticColsumParts);
+    dim3 g4((N + 127) / 128, kStaticColsumParts), g8((N + 255) / 256, kStaticColsumParts);
     // every [part][column < N] slot is written by the first kernel before the second reads it, so nothing left over
     // from an earlier call is ever consumed and no clearing is needed
-    if (dtype == F32) colsum_partial_kernel<float><<<g, 256, 0, st>>>((const float*)X, ld, M, N, scratch);
-    else if (dtype == BF16) colsum_partial_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)X, ld, M, N, scratch);
+    if (dtype == F32) colsum_partial_kernel<float><<<g4, 256, 0, st>>>((const float*)X, ld, M, N, scratch);
+    else if (dtype == BF16) colsum_partial_kernel<__nv_bfloat16><<<g8, 256, 0, st>>>((const __nv_bfloat16*)X, ld, M, N, scratch);
     else { set_error("colsum_static: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
     colsum_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>(scratch, kStaticColsumParts, N, out, accumulate);
     count_launch(2);

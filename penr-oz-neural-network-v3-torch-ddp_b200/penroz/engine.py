@@ -113,7 +113,9 @@ class Gpt2Engine:
         self.mode = None
         self._ws = {}
         self.grad_sync = None          # penroz.grad_sync.GradSync when world_size > 1
-        self.head_chunk_rows = int(os.environ.get("PENROZ_HEAD_CHUNK_ROWS", "4096"))
+        # rows of logits alive at once: 6144 = 24 CTA-pair tiles of 256 rows, so the chunk's dX GEMM (3 column tiles) is
+        # 72 units = one wave of the 74 CTA pairs; the [rows, 50304] bf16 chunk is 618 MB
+        self.head_chunk_rows = int(os.environ.get("PENROZ_HEAD_CHUNK_ROWS", "6144"))
         self.clip_grad_norm = float(os.environ.get("PENROZ_CLIP_GRAD_NORM", "0") or 0.0)
         self._err_flag = torch.zeros(1, device=self.device, dtype=torch.int32)
         self.keep_for_stats = None     # dict filled on stats epochs (rank 0)
