@@ -256,6 +256,8 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # rank 0 must print exactly ONE line: keep NCCL's version banner (NCCL_DEBUG=VERSION/INFO) off stdout
+    os.environ["NCCL_DEBUG"] = os.environ.get("PENROZ_NCCL_DEBUG", "WARN")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if world > 1:

@@ -307,11 +307,17 @@ struct AttnBwdSmem {
     static constexpr int kG0 = kQ0 + 2 * 16384;        // 2 x 16 KB  dO_i
     static constexpr int kP = kG0 + 2 * 16384;         // 32 KB  P   [2 key blocks][128 q][64]
     static constexpr int kDS = kP + 32768;             // 32 KB  dS  same layout
-    static constexpr int kBar = kDS + 32768;
-    static constexpr int kBytes = kBar + 128 + 1024;
+    static constexpr int kBar = kDS + 32768;           // barriers + tmem slot (128 B)
+    static constexpr int kStage = kBar + 128;          // 16 warps x [32 rows][17 floats]: dQ staging for coalesced red.add
+    static constexpr int kBytes = kStage + 16 * 32 * 17 * 4 + 1024;
 };
 
-__global__ void __launch_bounds__(320, 1)
+// 18 warps: 0-15 softmax-gradient (4 threads per query row: TMEM lane quarter = warp % 4, 32-key column slice =
+// warp / 4), 16 = MMA issuer, 17 = TMA producer. TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ x2 [384,512).
+// Per query tile `it`:   MMA: S,dP(it) ........ dV,dK,dQ(it) -> S,dP(it+1) ...
+//                        SM :        softmax-grad(it) -> P,dS | dQ(it-1) red.add | softmax-grad(it+1) ...
+// dQ is double buffered so the reduction of tile it-1 runs under the MMAs of tile it.
+__global__ void __launch_bounds__(576, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
                    __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2e) {
@@ -332,14 +338,14 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const int C = H * AT_D;
     const int n_it = n_qt - jt;                        // query tiles jt .. n_qt-1
 
-    if (threadIdx.x == 256) {
+    if (threadIdx.x == 512) {
         tma_prefetch_desc(&tmQKV);
         tma_prefetch_desc(&tmDO);
         mbar_init(kv_full, 1);
         mbar_init(qg_full0, 1); mbar_init(qg_full0 + 8, 1);
         mbar_init(qg_empty0, 1); mbar_init(qg_empty0 + 8, 1);
         mbar_init(sdp_full, 1);
-        mbar_init(pds_ready, 8);
+        mbar_init(pds_ready, 16);
         mbar_init(dq_full, 1);
         mbar_fence_init();
     }
@@ -353,7 +359,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const uint32_t tmem = *tmem_slot;
     const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 320, tDQ = tmem + 384;
 
-    if (warp == 9) {
+    if (warp == 17) {
         // ------------------------------------------------ TMA producer
         if (lane == 0) {
             mbar_expect_tx(kv_full, 32768);
@@ -369,7 +375,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             }
         }
         __syncwarp();
-    } else if (warp == 8) {
+    } else if (warp == 16) {
         // ------------------------------------------------ MMA issuer
         if (lane == 0) {
             const uint32_t sK = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV;
@@ -382,14 +388,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             // P/dS as MN-major A (dV, dK; 64-key blocks 16 KB apart) and dS as K-major A (dQ)
             const uint32_t k_lo = desc_lo(sK, 1), v_lo = desc_lo(sV, 1), km_lo = desc_lo(sK, 512);
             const uint32_t pm_lo = desc_lo(sP, 1024), dsm_lo = desc_lo(sDS, 1024), dsk_lo = desc_lo(sDS, 1);
-            mbar_wait(kv_full, 0);
-            for (int it = 0; it < n_it; ++it) {
+            auto issue_s_dp = [&](int it) {
                 const int s = it & 1;
-                const uint32_t sQ = sbase + AttnBwdSmem::kQ0 + s * 16384;
-                const uint32_t sG = sbase + AttnBwdSmem::kG0 + s * 16384;
+                const uint32_t q_lo = desc_lo(sbase + AttnBwdSmem::kQ0 + s * 16384, 1);
+                const uint32_t g_lo = desc_lo(sbase + AttnBwdSmem::kG0 + s * 16384, 1);
                 mbar_wait(qg_full0 + 8 * s, (uint32_t)((it >> 1) & 1));
                 tc_fence_after();
-                const uint32_t q_lo = desc_lo(sQ, 1), g_lo = desc_lo(sG, 1);
 #pragma unroll
                 for (int k4 = 0; k4 < 4; ++k4)   // S = Q K^T
                     umma_bf16(tS, desc_make(q_lo + k4 * 2, kHi), desc_make(k_lo + k4 * 2, kHi), id_kk128, (uint32_t)(k4 != 0));
@@ -397,9 +401,16 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 for (int k4 = 0; k4 < 4; ++k4)   // dP = dO V^T
                     umma_bf16(tDP, desc_make(g_lo + k4 * 2, kHi), desc_make(v_lo + k4 * 2, kHi), id_kk128, (uint32_t)(k4 != 0));
                 umma_commit(sdp_full);
-                mbar_wait(pds_ready, (uint32_t)(it & 1));
+            };
+            mbar_wait(kv_full, 0);
+            issue_s_dp(0);
+            for (int it = 0; it < n_it; ++it) {
+                const int s = it & 1;
+                const uint32_t qm_lo = desc_lo(sbase + AttnBwdSmem::kQ0 + s * 16384, 512);
+                const uint32_t gm_lo = desc_lo(sbase + AttnBwdSmem::kG0 + s * 16384, 512);
+                const uint32_t tDQb = tDQ + (uint32_t)(s * 64);
+                mbar_wait(pds_ready, (uint32_t)(it & 1));     // P, dS of this tile are in smem; S/dP TMEM is free again
                 tc_fence_after();
-                const uint32_t qm_lo = desc_lo(sQ, 512), gm_lo = desc_lo(sG, 512);
 #pragma unroll
                 for (int k8 = 0; k8 < 8; ++k8)   // dV += P^T dO   (M = keys, K = queries; both operands MN-major)
                     umma_bf16(tDV, desc_make(pm_lo + k8 * 128, kHi), desc_make(gm_lo + k8 * 128, kHi), id_mm64,
@@ -410,26 +421,52 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                               (uint32_t)((it | k8) != 0));
 #pragma unroll
                 for (int k8 = 0; k8 < 8; ++k8)   // dQ_i = dS K   (M = queries, K = keys)
-                    umma_bf16(tDQ, desc_make(dsk_lo + (k8 >> 2) * 1024 + (k8 & 3) * 2, kHi), desc_make(km_lo + k8 * 128, kHi),
+                    umma_bf16(tDQb, desc_make(dsk_lo + (k8 >> 2) * 1024 + (k8 & 3) * 2, kHi), desc_make(km_lo + k8 * 128, kHi),
                               id_km64, (uint32_t)(k8 != 0));
                 umma_commit(dq_full);
                 umma_commit(qg_empty0 + 8 * s);
+                if (it + 1 < n_it) issue_s_dp(it + 1);
             }
         }
         __syncwarp();
     } else {
-        // ------------------------------------------------ softmax-gradient threads: 8 warps, two threads per query row.
-        // TMEM lane quarter = warp % 4 (hardware rule); warps 0-3 take key columns 0..63 (key block 0), warps 4-7
-        // columns 64..127 (key block 1). lse and delta are precomputed, so the two halves never talk to each other.
-        const int qd = warp & 3, half = warp >> 2;
+        // ------------------------------------------------ softmax-gradient threads
+        const int qd = warp & 3, part = warp >> 2;          // lane quarter, 32-key column slice
         const int r = qd * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(qd * 32) << 16;
-        uint8_t* sPp = smem + AttnBwdSmem::kP;
-        uint8_t* sDSp = smem + AttnBwdSmem::kDS;
+        uint8_t* pb = smem + AttnBwdSmem::kP + (part >> 1) * 16384;
+        uint8_t* db = smem + AttnBwdSmem::kDS + (part >> 1) * 16384;
+        float* stg = reinterpret_cast<float*>(smem + AttnBwdSmem::kStage) + warp * (32 * 17);
         const float log2e = 1.44269504088896340736f;
         const size_t stat0 = ((size_t)b * H + h) * Tn;
         float lse_next = 0.f, dl_next = 0.f;
         if (jt * AT_BM + r < Tn) { lse_next = lse[stat0 + jt * AT_BM + r]; dl_next = delta[stat0 + jt * AT_BM + r]; }
+
+        // dQ of query tile `t` (TMEM buffer t & 1): 16 columns per thread -> staging -> row-coalesced red.add
+        auto reduce_dq = [&](int t) {
+            uint32_t v[16];
+            __syncwarp();
+            tmem_ld_32x16(tDQ + (uint32_t)((t & 1) * 64) + lane_addr + part * 16, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 16; ++k) stg[lane * 17 + k] = __uint_as_float(v[k]);
+            __syncwarp();
+            const int q0 = (jt + t) * AT_BM + qd * 32;       // first query row of this warp's 32
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int rr = 8 * k + (lane >> 2), cc = (lane & 3) * 4;
+                if (q0 + rr < Tn) {
+                    const float* d = stg + rr * 17 + cc;
+                    float* o = dq_accum + ((size_t)(b * Tn) + q0 + rr) * C + h * AT_D + part * 16 + cc;
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o), "f"(d[0]), "f"(d[1]), "f"(d[2]),
+                                 "f"(d[3])
+                                 : "memory");
+                }
+            }
+            __syncwarp();
+            tc_fence_before();
+        };
+
         for (int it = 0; it < n_it; ++it) {
             const int qt = jt + it;
             const int i = qt * AT_BM + r;               // query position
@@ -440,14 +477,15 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             else { lse_next = 0.f; dl_next = 0.f; }
             const bool diag = (it == 0);
             const bool edge = diag || ((qt + 1) * AT_BM > Tn);
-            const int key0 = jt * AT_BN;
+            const int key0 = jt * AT_BN + part * 32;
+            // the MMAs of the previous tile must be done with P/dS (and its dQ is complete) before they are overwritten
+            if (it > 0) { mbar_wait(dq_full, (uint32_t)((it - 1) & 1)); }
             mbar_wait(sdp_full, (uint32_t)(it & 1));
             tc_fence_after();
-#pragma unroll 1
-            for (int c = 2 * half; c < 2 * half + 2; ++c) {
+            {
                 uint32_t sv[32], dv[32];
-                tmem_ld_32x32(tS + lane_addr + c * 32, sv);
-                tmem_ld_32x32(tDP + lane_addr + c * 32, dv);
+                tmem_ld_32x32(tS + lane_addr + part * 32, sv);
+                tmem_ld_32x32(tDP + lane_addr + part * 32, dv);
                 tmem_ld_wait();
                 uint32_t pp[16], dd[16];
 #pragma unroll
@@ -455,19 +493,17 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                     float p0 = ex2_fast(fmaf(__uint_as_float(sv[k]), scale_log2e, -L2));
                     float p1 = ex2_fast(fmaf(__uint_as_float(sv[k + 1]), scale_log2e, -L2));
                     if (edge) {   // diagonal tile or a tile with rows past the sequence end: warp-uniform flag
-                        if (!row_ok || (diag && key0 + c * 32 + k > i)) p0 = 0.f;
-                        if (!row_ok || (diag && key0 + c * 32 + k + 1 > i)) p1 = 0.f;
+                        if (!row_ok || (diag && key0 + k > i)) p0 = 0.f;
+                        if (!row_ok || (diag && key0 + k + 1 > i)) p1 = 0.f;
                     }
                     const float d0 = p0 * (__uint_as_float(dv[k]) - dl) * scale;
                     const float d1 = p1 * (__uint_as_float(dv[k + 1]) - dl) * scale;
                     pp[k >> 1] = pack_bf16x2(p0, p1);
                     dd[k >> 1] = pack_bf16x2(d0, d1);
                 }
-                uint8_t* pb = sPp + (c >> 1) * 16384;
-                uint8_t* db = sDSp + (c >> 1) * 16384;
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4) {
-                    const uint32_t off = sw128_off(r, (c & 1) * 32 + q4 * 8);
+                    const uint32_t off = sw128_off(r, (part & 1) * 32 + q4 * 8);
                     *reinterpret_cast<uint4*>(pb + off) = make_uint4(pp[4 * q4], pp[4 * q4 + 1], pp[4 * q4 + 2], pp[4 * q4 + 3]);
                     *reinterpret_cast<uint4*>(db + off) = make_uint4(dd[4 * q4], dd[4 * q4 + 1], dd[4 * q4 + 2], dd[4 * q4 + 3]);
                 }
@@ -476,52 +512,32 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             fence_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(pds_ready);
-            mbar_wait(dq_full, (uint32_t)(it & 1));
-            tc_fence_after();
-            float* dq = dq_accum + ((size_t)(b * Tn) + (row_ok ? i : 0)) * C + h * AT_D;
-#pragma unroll 1
-            for (int c = half; c < half + 1; ++c) {
-                uint32_t v[32];
-                __syncwarp();
-                tmem_ld_32x32(tDQ + lane_addr + c * 32, v);
-                tmem_ld_wait();
-                if (row_ok) {
-#pragma unroll
-                    for (int k = 0; k < 32; k += 4)
-                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq + c * 32 + k),
-                                     "f"(__uint_as_float(v[k])), "f"(__uint_as_float(v[k + 1])),
-                                     "f"(__uint_as_float(v[k + 2])), "f"(__uint_as_float(v[k + 3]))
-                                     : "memory");
-                }
-            }
-            __syncwarp();
-            tc_fence_before();
+            if (it > 0) { tc_fence_after(); reduce_dq(it - 1); }   // runs under this tile's dV/dK/dQ MMAs
         }
-        // dV, dK of this key tile: lane = key row
+        mbar_wait(dq_full, (uint32_t)((n_it - 1) & 1));
+        tc_fence_after();
+        reduce_dq(n_it - 1);
+        // dV, dK of this key tile: lane = key row, 16 columns per thread
         const int key = jt * AT_BN + r;
         const bool key_ok = key < Tn;
-        __nv_bfloat16* gk = dqkv + ((size_t)(b * Tn) + (key_ok ? key : 0)) * 3 * C + C + h * AT_D;
+        __nv_bfloat16* gk = dqkv + ((size_t)(b * Tn) + (key_ok ? key : 0)) * 3 * C + C + h * AT_D + part * 16;
         __nv_bfloat16* gv = gk + C;
 #pragma unroll 1
         for (int which = 0; which < 2; ++which) {
-            const uint32_t taddr = which == 0 ? tDV : tDK;
-            __nv_bfloat16* dst = which == 0 ? gv : gk;
-#pragma unroll 1
-            for (int c = half; c < half + 1; ++c) {
-                uint32_t v[32];
-                __syncwarp();
-                tmem_ld_32x32(taddr + lane_addr + c * 32, v);
-                tmem_ld_wait();
-                if (key_ok) {
+            uint32_t v[16];
+            __syncwarp();
+            tmem_ld_32x16((which == 0 ? tDV : tDK) + lane_addr + part * 16, v);
+            tmem_ld_wait();
+            if (key_ok) {
+                __nv_bfloat16* dst = which == 0 ? gv : gk;
 #pragma unroll
-                    for (int k = 0; k < 32; k += 8) {
-                        uint4 w;
-                        w.x = pack_bf16x2(__uint_as_float(v[k]), __uint_as_float(v[k + 1]));
-                        w.y = pack_bf16x2(__uint_as_float(v[k + 2]), __uint_as_float(v[k + 3]));
-                        w.z = pack_bf16x2(__uint_as_float(v[k + 4]), __uint_as_float(v[k + 5]));
-                        w.w = pack_bf16x2(__uint_as_float(v[k + 6]), __uint_as_float(v[k + 7]));
-                        *reinterpret_cast<uint4*>(dst + c * 32 + k) = w;
-                    }
+                for (int k = 0; k < 16; k += 8) {
+                    uint4 w;
+                    w.x = pack_bf16x2(__uint_as_float(v[k]), __uint_as_float(v[k + 1]));
+                    w.y = pack_bf16x2(__uint_as_float(v[k + 2]), __uint_as_float(v[k + 3]));
+                    w.z = pack_bf16x2(__uint_as_float(v[k + 4]), __uint_as_float(v[k + 5]));
+                    w.w = pack_bf16x2(__uint_as_float(v[k + 6]), __uint_as_float(v[k + 7]));
+                    *reinterpret_cast<uint4*>(dst + k) = w;
                 }
             }
         }
@@ -625,7 +641,7 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     attn_bwd_delta_kernel<<<(unsigned)((pairs * 8 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
-    attn_bwd_tc_kernel<<<grid, 320, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
+    attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
     size_t n4 = rows * C / 4;
     size_t g = (n4 + 255) / 256;
     size_t cap = (size_t)num_sms() * 16;

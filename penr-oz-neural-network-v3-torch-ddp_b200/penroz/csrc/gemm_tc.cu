@@ -812,17 +812,29 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
 
     const int sms = num_sms();
     const int tiles_m = (M + BM - 1) / BM;
-    // wide tiles when they still give every SM work; otherwise the 128-wide tile (more CTAs in flight)
+    // Tile shape: estimate the number of waves of each configuration, weighted by the work one wave does per SM and
+    // by the measured efficiency of that kernel (pair 256x256 > single 128x256 > single 128x128), and take the
+    // cheapest. The weight-gradient form (split-K supplies parallelism) always takes the widest tile that fits.
+    auto ceil_div = [](long long a, long long b) { return (a + b - 1) / b; };
+    const long long u_pair = ceil_div(M, 2 * BM) * ceil_div(N, 256);
+    const long long u_256 = (long long)tiles_m * ceil_div(N, 256);
+    const long long u_128 = (long long)tiles_m * ceil_div(N, 128);
+    const bool pair_ok = (M >= 256) && (N > 128) && (sms >= 2) && !(flags & 16);
+    const double c_pair = pair_ok ? (double)ceil_div(u_pair, sms / 2) * 1.0 : 1e30;
+    const double c_256 = (N > 128) ? (double)ceil_div(u_256, sms) * 1.12 : 1e30;
+    const double c_128 = (double)ceil_div(u_128, sms) * 0.5 * 1.35;
     int bn = 256;
-    if (N <= 128) bn = 128;
-    // few output tiles: narrower tiles put more CTAs to work — except for the weight-gradient form, where split-K
-    // supplies the parallelism and the wide tile moves 25 % fewer operand bytes through L2 per flop
-    else if (epilogue != EPI_ACCUM_F32 && (long long)tiles_m * ((N + 255) / 256) < sms) bn = 128;
-    if (flags & 4) bn = 128;
-    if (flags & 8) bn = 256;
-    // CTA pairs (256 x 256 tiles, cta_group::2) whenever the problem has at least one full pair tile; flags bit 4 forces
-    // the single-CTA kernel (used by the tests to cover both)
-    const bool pair = (bn == 256) && (M >= 256) && !(flags & 16) && (sms >= 2);
+    bool pair = false;
+    if (epilogue == EPI_ACCUM_F32) {
+        pair = pair_ok;
+        bn = (N > 128) ? 256 : 128;
+    } else if (c_pair <= c_256 && c_pair <= c_128) {
+        pair = true;
+    } else if (c_128 < c_256) {
+        bn = 128;
+    }
+    if (flags & 4) { bn = 128; pair = false; }
+    if (flags & 8) { bn = 256; pair = pair_ok; }
     p.tiles_m = pair ? (M + 2 * BM - 1) / (2 * BM) : tiles_m;
     p.tiles_n = (N + bn - 1) / bn;
     p.kb_total = (K + BK - 1) / BK;

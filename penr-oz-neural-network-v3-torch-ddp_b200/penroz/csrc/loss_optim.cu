@@ -90,6 +90,74 @@ ce_rows_kernel(T* __restrict__ logits, long long ld, const long long* __restrict
     }
 }
 
+// bf16 rows that fit in shared memory (V * 2 bytes <= ~110 KB, two CTAs per SM): the row is read from HBM ONCE into
+// smem while (max, sum-exp) are accumulated, then the gradient is produced from the smem copy. Algorithmic traffic
+// per row: V*2 read + V*2 written (the two-pass kernel above reads the row twice).
+__global__ void __launch_bounds__(512)
+ce_rows_smem_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const long long* __restrict__ tgt, int V,
+                    long long ignore_index, const int* __restrict__ n_valid, float grad_scale,
+                    float* __restrict__ loss_rows, int* __restrict__ err_flag) {
+    extern __shared__ uint4 rowbuf[];
+    __shared__ float red[32];
+    const int row = blockIdx.x;
+    __nv_bfloat16* x = logits + (size_t)row * ld;
+    const long long t = tgt[row];
+    const bool ignored = (t == ignore_index);
+    if (!ignored && (t < 0 || t >= V)) {
+        if (threadIdx.x == 0 && err_flag) atomicExch(err_flag, 2);
+    }
+    const int nvec = V >> 3;
+    uint4* x4 = reinterpret_cast<uint4*>(x);
+    float m = -INFINITY, s = 0.f;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+        Vec16<__nv_bfloat16> v;
+        v.raw = x4[i];
+        rowbuf[i] = v.raw;
+        float lm = v.get(0);
+#pragma unroll
+        for (int k = 1; k < 8; ++k) lm = fmaxf(lm, v.get(k));
+        const float nm = fmaxf(m, lm);
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc += __expf(v.get(k) - nm);
+        s = s * __expf(m - nm) + acc;
+        m = nm;
+    }
+    for (int i = nvec * 8 + threadIdx.x; i < V; i += blockDim.x) {   // < 8 tail elements
+        const float v = __bfloat162float(x[i]);
+        const float nm = fmaxf(m, v);
+        s = s * __expf(m - nm) + __expf(v - nm);
+        m = nm;
+    }
+    const float gm = block_max(m, red);
+    const float part = (m == -INFINITY) ? 0.f : s * __expf(m - gm);
+    const float gs = block_sum(part, red);
+    const float lse = gm + logf(gs);
+    if (threadIdx.x == 0) {
+        float l = 0.f;
+        if (!ignored && t >= 0 && t < V) l = lse - __bfloat162float(x[t]);
+        loss_rows[row] = l;
+    }
+    __syncthreads();  // x[t] read above before the row is overwritten
+    const float scale = ignored ? 0.f : grad_scale / (float)max(1, *n_valid);
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+        Vec16<__nv_bfloat16> v;
+        v.raw = rowbuf[i];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float p = __expf(v.get(k) - lse);
+            if ((long long)(i * 8 + k) == t) p -= 1.f;
+            v.set(k, p * scale);
+        }
+        x4[i] = v.raw;
+    }
+    for (int i = nvec * 8 + threadIdx.x; i < V; i += blockDim.x) {
+        float p = __expf(__bfloat162float(x[i]) - lse);
+        if ((long long)i == t) p -= 1.f;
+        x[i] = __float2bfloat16_rn(p * scale);
+    }
+}
+
 // loss = sum(loss_rows) / n_valid, single CTA, fixed order (deterministic); *loss_out (+)= loss * out_scale
 __global__ void ce_reduce_kernel(const float* __restrict__ loss_rows, int M, const int* __restrict__ n_valid,
                                  float out_scale, float* __restrict__ loss_out, int accumulate) {
@@ -216,7 +284,18 @@ extern "C" int penroz_ce_rows(void* logits, long long ld, const long long* targe
     PENROZ_REQUIRE(logits && targets && loss_rows && n_valid, "ce_rows: null argument");
     cudaStream_t st = (cudaStream_t)stream;
     const int threads = V >= 8192 ? 512 : (V >= 1024 ? 256 : 64);
-    if (dtype == BF16)
+    const size_t row_smem = ((size_t)(V >> 3)) * 16;
+    if (dtype == BF16 && write_grad && V >= 4096 && row_smem <= 110 * 1024 && (ld % 8 == 0) && ((uintptr_t)logits % 16 == 0)) {
+        static std::atomic<int> configured{0};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (!((configured.load() >> dev) & 1)) {
+            cudaError_t e = cudaFuncSetAttribute(ce_rows_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e != cudaSuccess) { set_error("ce_rows: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+            configured.fetch_or(1 << dev);
+        }
+        ce_rows_smem_kernel<<<M, 512, row_smem, st>>>((__nv_bfloat16*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, err_flag);
+    } else if (dtype == BF16)
         ce_rows_kernel<__nv_bfloat16><<<M, threads, 0, st>>>((__nv_bfloat16*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, write_grad, err_flag);
     else if (dtype == F32)
         ce_rows_kernel<float><<<M, threads, 0, st>>>((float*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, write_grad, err_flag);
