@@ -319,6 +319,15 @@ def run_ours(args):
     value = world * B * T / (ms_per_step / 1e3)
     final_loss = loss.item()
 
+    parts = os.environ.get("PENROZ_BENCH_PARTS", "all")   # "value": only the timed loop (short runs under ncu)
+    if parts == "value":
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                              "warmup": args.warmup, "ms_per_step": ms_per_step, "gpu_launches": int(launches),
+                              "note": "PENROZ_BENCH_PARTS=value: timed loop only"}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
     # ---------------- roofline: event pairs around each launch of the big kernel families, one extra step
     roofline = None
     if rank == 0:

@@ -494,22 +494,26 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // traffic per flop through L2 drops by a third and the smem ring gets 6 stages deep. The even CTA issues every
 // tcgen05.mma.cta_group::2 (M = 256) and owns the full / tmem-empty barriers; completion of MMAs is multicast to both
 // CTAs' empty / tmem-full barriers. Epilogue code is shared with the single-CTA kernel.
-struct GemmCfg2 {
+// EW = epilogue warps per CTA: 8 for light epilogues (6 smem stages), 16 for the activation-math epilogues (GELU,
+// GELU'), whose instruction count per tile exceeds the mainloop's duration with 8 warps (4 stages leave room for the
+// 16 staging tiles).
+template <int EW> struct GemmCfg2 {
     static constexpr int BN = 256;
     static constexpr int kABytes = BM * BK * 2;            // 128 rows of A
     static constexpr int kBBytes = (BN / 2) * BK * 2;      // this CTA's half of B
     static constexpr int kStageBytes = kABytes + kBBytes;  // 32 KB
-    static constexpr int kStages = 6;
+    static constexpr int kStages = (EW == 16) ? 4 : 6;
     static constexpr int kTmemCols = 2 * BN;
-    static constexpr int kStagingBytes = 8 * 32 * 33 * 4;
+    static constexpr int kStagingBytes = EW * 32 * 33 * 4;
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kStagingBytes;
+    static constexpr int kThreads = (4 + EW) * 32;
 };
 
-template <int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
+template <int EPI, int EW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((4 + EW) * 32, 1)
 gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const GemmParams p) {
-    using Cfg = GemmCfg2;
+    using Cfg = GemmCfg2<EW>;
     constexpr int BN = Cfg::BN;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
@@ -539,7 +543,7 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);    // one multicast commit
-            mbar_init(tempty_bar(s), 16);  // 8 epilogue warps of each CTA (only the leader's copy is used)
+            mbar_init(tempty_bar(s), 2 * EW);  // every epilogue warp of both CTAs (only the leader's copy is used)
         }
         mbar_fence_init();
     }
@@ -633,7 +637,8 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         // ------------------------------------------------------------ epilogue (both CTAs, own 128 accumulator rows)
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
-        constexpr int kChunks = BN / 64;
+        constexpr int kChunks = BN / 32 / (EW / 4);   // EW / 4 column slices
+        constexpr bool kPrefetch = (EW == 8);         // with 16 warps the extra registers cost more than the latency
         float* stg = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256) + (warp - 4) * (32 * 33);
         int as = 0;
         uint32_t aph = 0;
@@ -647,7 +652,7 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             bool pre_valid = false;
             {
                 const int c0 = n0 + half * kChunks * 32;
-                if (kHasAux && row0 < p.M && c0 < p.N && chunk_is_fast<EPI>(p, c0)) {
+                if (kPrefetch && kHasAux && row0 < p.M && c0 < p.N && chunk_is_fast<EPI>(p, c0)) {
                     aux_issue<EPI>(p, pre, lane, row0, c0);
                     pre_valid = true;
                 }
@@ -668,7 +673,7 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
                 int next_col0 = -1;
-                if (kHasAux && cc + 1 < kChunks && col0 + 32 < p.N && chunk_is_fast<EPI>(p, col0 + 32)) next_col0 = col0 + 32;
+                if (kPrefetch && kHasAux && cc + 1 < kChunks && col0 + 32 < p.N && chunk_is_fast<EPI>(p, col0 + 32)) next_col0 = col0 + 32;
                 epilogue_chunk<EPI>(p, acc, stg, lane, row0, col0, full, pre, pre_valid, next_col0);
                 pre_valid = (next_col0 >= 0);
             }
@@ -741,16 +746,18 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
 
 template <int EPI>
 static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
-    auto kern = gemm_bf16_tc2_kernel<EPI>;
+    constexpr int EW = (EPI == EPI_GELU || EPI == EPI_DGELU) ? 16 : 8;
+    using Cfg2 = GemmCfg2<EW>;
+    auto kern = gemm_bf16_tc2_kernel<EPI, EW>;
     static std::atomic<int> configured{0};
     int dev = 0;
     cudaGetDevice(&dev);
     if (!((configured.load() >> dev) & 1)) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg2::kSmemBytes);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2::kSmemBytes);
         if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
         configured.fetch_or(1 << dev);
     }
-    kern<<<grid, 384, GemmCfg2::kSmemBytes, st>>>(tmA, tmB, p);
+    kern<<<grid, Cfg2::kThreads, Cfg2::kSmemBytes, st>>>(tmA, tmB, p);
     count_launch();
     return check_launch("gemm_bf16_tc2");
 }
