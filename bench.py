@@ -49,6 +49,19 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+def ncu_traffic_per_launch(family: str):
+    """Mean DRAM bytes per launch of a kernel family, from the committed ncu launch list of this same command."""
+    path = os.path.join(ROOT, "profiles", "r01_ncu_launch_list_step.json")
+    try:
+        fams = json.load(open(path))["families"]
+    except Exception:
+        return None
+    key = "gemm_bf16" if family.startswith("gemm") else "attn_"
+    sel = [f for f in fams if f["kernel"].startswith(key) and "delta" not in f["kernel"] and "finish" not in f["kernel"]]
+    n = sum(f["launches"] for f in sel)
+    return (sum(f["dram_read_MB"] + f["dram_write_MB"] for f in sel) * 1e6 / n) if n else None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -345,7 +358,9 @@ def run_ours(args):
         achieved = d["flops"] / (d["ms"] / 1e3) / 1e12
         peak = peaks["bf16_tflops_sustained"]
         roofline = {"kernel": name, "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": f"{which} (sustained: kernel timed inside a long step)",
+                    "frac": achieved / peak, "traffic": ncu_traffic_per_launch(name),
+                    "traffic_source": "profiles/r01_ncu_launch_list_step.json (dram__bytes_read+write per launch, family mean)",
+                    "peak_source": f"{which} (sustained: kernel timed inside a long step)",
                     "share_of_step": d["ms"] / step_ms, "launches_per_step": d["launches"],
                     "families_ms": {k: round(v["ms"], 3) for k, v in fam.items()}, "instrumented_step_ms": step_ms}
     else:

@@ -717,6 +717,33 @@ class _FusedStepper:
     def __init__(self, model: NeuralNetworkModel, engine, device, use_amp: bool):
         self.model, self.engine, self.device, self.use_amp = model, engine, device, use_amp
         self.sync_mode = os.environ.get("PENROZ_ACCUM_SYNC", "reference")
+        self._pinned = None      # two pinned (x, y) staging pairs, reused round-robin
+        self._copied = None      # CUDA events: the H2D copy out of each pair has finished
+        self._slot = 0
+
+    def _upload(self, arrays, batch_size, block_size):
+        """Loader window (int32 numpy) -> int64 device tensors through pinned host memory, copy enqueued
+        asynchronously on the compute stream (the reference does a synchronous pageable copy per tensor,
+        neural_net_model.py:630-631)."""
+        if self._pinned is None:
+            self._pinned = [[torch.empty((batch_size, block_size), dtype=torch.long).pin_memory() for _ in range(2)]
+                            for _ in range(2)]
+            self._copied = [None, None]
+        slot = self._slot
+        self._slot ^= 1
+        if self._copied[slot] is not None:
+            self._copied[slot].synchronize()      # the previous copy out of this pair is done: safe to overwrite
+        out = []
+        for host, arr in zip(self._pinned[slot], arrays):
+            if host.shape != (batch_size, block_size):
+                self._pinned = None
+                return self._upload(arrays, batch_size, block_size)
+            host.view(-1).copy_(torch.from_numpy(arr))     # int32 -> int64 widening on the host, 256 KB
+            out.append(host.to(self.device, non_blocking=True))
+        ev = torch.cuda.Event()
+        ev.record()
+        self._copied[slot] = ev
+        return out
 
     def begin(self):
         from penroz._lib import PenrozError
@@ -750,8 +777,7 @@ class _FusedStepper:
         cost = torch.tensor(0.0).to(self.device)
         pairs = []
         for step in range(num_steps):
-            x, y = (torch.from_numpy(arr.astype('int64', copy=False)).view(batch_size, block_size)
-                    .to(self.device, non_blocking=True) for arr in loader.next_batch())
+            x, y = self._upload(loader.next_batch(), batch_size, block_size)
             keep = want_stats and step == 0
             eng.keep_for_stats = {} if keep else None
             # which micro-step carries the gradient exchange: the reference arms DDP one step late, so with

@@ -744,9 +744,8 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     return check_launch("gemm_bf16_tc");
 }
 
-template <int EPI>
-static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
-    constexpr int EW = (EPI == EPI_GELU || EPI == EPI_DGELU) ? 16 : 8;
+template <int EPI, int EW>
+static int launch_gemm2_ew(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
     using Cfg2 = GemmCfg2<EW>;
     auto kern = gemm_bf16_tc2_kernel<EPI, EW>;
     static std::atomic<int> configured{0};
@@ -760,6 +759,14 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ge
     kern<<<grid, Cfg2::kThreads, Cfg2::kSmemBytes, st>>>(tmA, tmB, p);
     count_launch();
     return check_launch("gemm_bf16_tc2");
+}
+// 16 epilogue warps where the epilogue, not the mainloop, sets the tile time: the activation-math epilogues always,
+// the fp32 residual epilogue (256 KB of global traffic per tile) when the reduction is short
+template <int EPI>
+static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
+    if (EPI == EPI_GELU || EPI == EPI_DGELU) return launch_gemm2_ew<EPI, 16>(tmA, tmB, p, grid, st);
+    if (EPI == EPI_RESID_F32 && p.K <= 1024) return launch_gemm2_ew<EPI_RESID_F32, 16>(tmA, tmB, p, grid, st);
+    return launch_gemm2_ew<EPI, 8>(tmA, tmB, p, grid, st);
 }
 static int dispatch_epi2(int epi, const CUtensorMap& a, const CUtensorMap& b, const GemmParams& p, int grid, cudaStream_t st) {
     switch (epi) {

@@ -311,18 +311,27 @@ layernorm_bwd_cols_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, c
     }
 }
 
-// out_q[c] += sum_blocks scratch[b][q][c]   (fixed order: deterministic)
-__global__ void layernorm_bwd_reduce_kernel(const float* __restrict__ scratch, int nblocks, int C,
-                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                            float* __restrict__ dcol) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+// out_q[c] += sum_blocks scratch[b][q][c]   (fixed summation order: deterministic). 32 columns x 8 partial-sum
+// lanes per CTA, so the ~300 per-block partials are read by 8 threads per column instead of one.
+__global__ void __launch_bounds__(256)
+layernorm_bwd_reduce_kernel(const float* __restrict__ scratch, int nblocks, int C, float* __restrict__ dgamma,
+                            float* __restrict__ dbeta, float* __restrict__ dcol) {
+    __shared__ float sm[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
     const int qn = blockIdx.y;
     float* dst = (qn == 0) ? dgamma : (qn == 1) ? dbeta : dcol;
-    if (!dst) return;
     float s = 0.f;
-    for (int b = 0; b < nblocks; ++b) s += scratch[((size_t)b * 3 + qn) * C + c];
-    dst[c] += s;
+    if (dst && c < C)
+        for (int b = ty; b < nblocks; b += 8) s += scratch[((size_t)b * 3 + qn) * C + c];
+    sm[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && dst && c < C) {
+        float t = sm[0][tx];
+#pragma unroll
+        for (int k = 1; k < 8; ++k) t += sm[k][tx];
+        dst[c] += t;
+    }
 }
 
 // ------------------------------------------------------------------ GELU
@@ -559,7 +568,7 @@ int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const f
 #undef LN_BWD
     }
     if (rc != 0) { set_error("layernorm_bwd: no kernel for C=%d", C); return PENROZ_ERR_ARG; }
-    dim3 rg((C + 255) / 256, fuse_dcol ? 3 : 2);
+    dim3 rg((C + 31) / 32, fuse_dcol ? 3 : 2);
     layernorm_bwd_reduce_kernel<<<rg, 256, 0, st>>>(scratch, grid, C, dgamma, dbeta, fuse_dcol ? dcol : nullptr);
     count_launch(2);
     int e = check_launch("layernorm_bwd");

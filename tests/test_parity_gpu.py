@@ -159,3 +159,33 @@ def test_gpt2_small_slice_fp32_and_amp(env, golden, monkeypatch):
                 assert abs(float(v.double().sum()) - meta["slice"]["final_param_sum"][k]) < 1e-3 * max(1.0, abs(meta["slice"]["final_param_sum"][k])) + 0.5, k
         else:
             assert np.abs(np.array(losses) - g["slice/loss3"]).max() < 5e-2, losses
+
+
+@pytest.mark.parametrize("name,L,H,C", [("gpt2-medium-350M layout", 2, 16, 1024), ("gpt2-xl-1.5B layout", 2, 25, 1600)])
+def test_other_baseline_layouts_bf16_tracks_fp32(env, name, L, H, C):
+    """BASELINE configs 3 and 5 use C=1024/H=16 and C=1600/H=25 (head_dim 64, V=50257, T=1024). No reference golden
+    exists at these sizes (the CPU reference needs minutes per step), so the size-independent check is: on identical
+    weights and tokens the bf16 tensor-core path must track the exact fp32 path (itself pinned to the reference at the
+    tiny and 124M-slice sizes) — first loss to 2e-2, loss after 3 optimizer steps to 5e-2 — with depth cut to 2 blocks."""
+    T, V, B = 1024, 50257, 2
+    g = torch.Generator().manual_seed(C)
+    toks = torch.randint(0, V, (B * T + 1,), generator=g)
+    x = toks[:-1].view(B, T).to(env)
+    y = toks[1:].view(B, T).to(env)
+    losses = {}
+    for use_amp in (False, True):
+        m = build_gpt(f"lay{C}", L, H, C, T, V, seed=3)
+        m.to("cuda")
+        eng = m._engine()
+        eng.setup_training(use_amp=use_amp)
+        ls = []
+        for _ in range(3):
+            eng.zero_grad()
+            ls.append(eng.train_micro_step(x, y, 1.0).item())
+            eng.optimizer_step()
+        losses[use_amp] = ls
+        del m, eng
+        torch.cuda.empty_cache()
+    assert all(np.isfinite(losses[True])) and losses[False][2] < losses[False][0]
+    assert abs(losses[True][0] - losses[False][0]) < 2e-2, losses
+    assert abs(losses[True][2] - losses[False][2]) < 5e-2, losses
