@@ -171,6 +171,25 @@ int penroz_skinny_linear(const void* x, long long ldx, const void* W, long long 
                          int N, int K, int epilogue, int flags, int dtype, void* stream);
 int penroz_argmax_rows(const void* x, long long ld, int rows, int V, long long* out, int dtype, void* stream);
 
+/* ---- one whole single-token decode step of a GPT-2 tree, enqueued with a single host call ----
+ * Replaces one iteration of the generation loop (neural_net_model.py:465-469, incremental branch :382-386): embedding
+ * at position `pos`, every block (LN, QKV, paged K/V append at `pos`, split-KV attention over pos+1 keys, proj+residual,
+ * LN, fc+GELU, proj2+residual), final LN, LM head into logits_out [B,V] (model dtype) and, when argmax_out is not NULL,
+ * the greedy token ids. `layers` is a HOST array; every pointer inside it is a device pointer. */
+typedef struct penroz_gpt2_layer_t {
+    const void *ln1_w, *ln1_b, *qkv_w, *qkv_b, *proj_w, *proj_b, *ln2_w, *ln2_b, *fc_w, *fc_b, *proj2_w, *proj2_b;
+    void* kv_pool;
+    float ln1_eps, ln2_eps;
+    int gelu_tanh, ffn;
+} penroz_gpt2_layer_t;
+size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F, int t_len_max);
+int penroz_gpt2_decode_step(const long long* tokens, const void* wte, const void* wpe,
+                            const penroz_gpt2_layer_t* layers, int n_layer, const void* lnf_w, const void* lnf_b,
+                            float lnf_eps, const void* head_w, const void* head_b, const int* block_table,
+                            int max_pages, int B, int C, int H, int V, int pos, int dtype, void* workspace,
+                            size_t workspace_bytes, void* logits_out, long long* argmax_out, int* err_flag,
+                            void* stream);
+
 #ifdef __cplusplus
 }
 #endif

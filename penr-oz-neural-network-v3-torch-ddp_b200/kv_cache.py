@@ -147,6 +147,15 @@ class KVCache:
     def commit(self, n_tokens: int):
         self._paged.length += n_tokens
 
+    def account_tokens(self, n_tokens: int, bytes_per_layer: int, n_layers: int):
+        """Metrics for appends done inside the native decode step (one append per layer, as append() counts them)."""
+        m = self._metrics
+        m.num_appends += n_layers
+        m.total_entries += n_tokens * n_layers
+        m.memory_bytes += bytes_per_layer * n_layers
+        m.compressed_memory_bytes = m.memory_bytes
+        m.compression_ratio = 1.0
+
 
 class _PagedStore:
     def __init__(self, num_layers, B, H, D, dtype, device, capacity_hint):
@@ -178,12 +187,16 @@ class _PagedStore:
         for i, p in enumerate(self.pools):
             extra = torch.empty(add, 2, self.H, self.PAGE, self.D, device=self.device, dtype=self.dtype)
             self.pools[i] = torch.cat([p, extra], dim=0)
+        self.native_layers = None      # page pools moved: the native decode step's pointer table is stale
         self.free = list(range(self.n_pages + add - 1, self.n_pages - 1, -1)) + self.free
         self.n_pages += add
         table = torch.zeros((self.B, new_max), dtype=torch.int32)
         table[:, :self.max_pages] = self.table_host
         self.table_host = table
         self.max_pages = new_max
+
+    def ensure_pages(self, upto_tokens: int):
+        self._ensure(upto_tokens)
 
     def _ensure(self, upto_tokens: int):
         need = (upto_tokens + self.PAGE - 1) // self.PAGE

@@ -399,13 +399,19 @@ class NeuralNetworkModel(nn.Module):
             pl = self._plan
             kv_cache.paged(B, pl.n_head, pl.head_dim, pl.wte.weight.dtype, model_input.device,
                            capacity_hint=min(block_size, pl.block_size))
-            logits, _, _ = engine.forward_infer(model_input.contiguous(), None, pos_offset=offset, kv=kv_cache,
-                                                last_only=True)
+            greedy_ids = None
+            if model_input.shape[1] == 1:      # incremental step: one native call enqueues the whole token step
+                logits, greedy_ids = engine.decode_step(model_input, offset, kv_cache)
+            else:
+                logits, _, _ = engine.forward_infer(model_input.contiguous(), None, pos_offset=offset, kv=kv_cache,
+                                                    last_only=True)
         else:
             activations, _ = self(model_input, skip_softmax=True)
             logits = activations[-1]
         if temperature == 0.0:
             if fused:
+                if greedy_ids is not None:
+                    return greedy_ids
                 from penroz import ops
                 return ops.argmax_rows(logits.view(logits.shape[0], -1)).view(-1, 1)
             return logits[:, -1, :].argmax(dim=-1, keepdim=True)

@@ -302,3 +302,93 @@ extern "C" int penroz_argmax_rows(const void* x, long long ld, int rows, int V, 
     count_launch();
     return check_launch("argmax_rows");
 }
+
+// ------------------------------------------------------------------ whole single-token step, enqueued from C++
+// The decode step of a GPT-2 tree is ~9 kernels per block; driving them one ctypes call at a time costs more host
+// time than the GPU needs for the token (B = 1). This entry point enqueues the whole step — embedding, every
+// block (LN, QKV, paged K/V append, split-KV attention, proj + residual, LN, fc + GELU, proj2 + residual), final LN,
+// LM head, argmax — with one host call, using the same kernels as the individual entry points.
+// Replaces one iteration of the loop at neural_net_model.py:465-469 / 499-503 (incremental branch :382-386).
+extern "C" {
+int penroz_embed_fwd(const long long*, const void*, const void*, void*, int, int, int, int, int, int, int, int*, void*);
+int penroz_layernorm_fwd(const void*, const void*, const void*, void*, float*, float*, int, int, float, int, int, int, void*);
+int penroz_gemm_bf16(const void*, long long, int, const void*, long long, int, int, int, int, int, const void*, void*,
+                     long long, void*, long long, const void*, long long, int, void*);
+int penroz_gemm_f32(const float*, long long, int, const float*, long long, int, int, int, int, int, const float*, float*,
+                    long long, float*, long long, const float*, long long, int, void*);
+}
+
+struct penroz_gpt2_layer_t {
+    const void *ln1_w, *ln1_b, *qkv_w, *qkv_b, *proj_w, *proj_b, *ln2_w, *ln2_b, *fc_w, *fc_b, *proj2_w, *proj2_b;
+    void* kv_pool;
+    float ln1_eps, ln2_eps;
+    int gelu_tanh, ffn;
+};
+
+namespace penroz {
+// y = epi(x W^T + b): skinny kernel for few rows, tensor-core / FP32-pipe GEMM otherwise. epi: 0 store, 1 gelu, 2 resid
+static int decode_linear(const void* x, const void* W, const void* b, void* out, const void* aux, int M, int N, int K,
+                         int epi, int tanh_, int dtype, void* scratch_pre, void* stream) {
+    const int skinny_rows = (dtype == F32) ? 64 : 16;
+    if (M <= skinny_rows)
+        return penroz_skinny_linear(x, K, W, K, b, out, N, aux, N, nullptr, 0, M, N, K, epi, tanh_, dtype, stream);
+    if (dtype == BF16) {
+        if (epi == 1) return penroz_gemm_bf16(x, K, 0, W, K, 0, M, N, K, 1, b, scratch_pre, N, out, N, nullptr, 0, tanh_, stream);
+        return penroz_gemm_bf16(x, K, 0, W, K, 0, M, N, K, epi == 2 ? 3 : 0, b, out, N, nullptr, 0, aux, N, 0, stream);
+    }
+    if (epi == 1) return penroz_gemm_f32((const float*)x, K, 0, (const float*)W, K, 0, M, N, K, 1, (const float*)b, (float*)scratch_pre, N, (float*)out, N, nullptr, 0, tanh_, stream);
+    return penroz_gemm_f32((const float*)x, K, 0, (const float*)W, K, 0, M, N, K, epi == 2 ? 2 : 0, (const float*)b, (float*)out, N, nullptr, 0, (const float*)aux, N, 0, stream);
+}
+}  // namespace penroz
+
+extern "C" size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F, int t_len_max) {
+    const size_t es = 4;  // sized for fp32; bf16 uses half of the activation part
+    const size_t act = (size_t)B * ((size_t)2 * C + C + 3 * C + C + 2 * (size_t)F + C) * es;
+    return act + penroz_attn_decode_scratch_bytes(B, H, C / H, t_len_max) + 256;
+}
+
+extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte, const void* wpe,
+                                       const penroz_gpt2_layer_t* layers, int n_layer, const void* lnf_w,
+                                       const void* lnf_b, float lnf_eps, const void* head_w, const void* head_b,
+                                       const int* block_table, int max_pages, int B, int C, int H, int V, int pos,
+                                       int dtype, void* workspace, size_t workspace_bytes, void* logits_out,
+                                       long long* argmax_out, int* err_flag, void* stream) {
+    PENROZ_REQUIRE(B > 0 && C > 0 && H > 0 && V > 0 && n_layer > 0 && pos >= 0, "gpt2_decode_step: bad shape");
+    PENROZ_REQUIRE(C % H == 0, "gpt2_decode_step: n_embd %d not divisible by %d heads", C, H);
+    PENROZ_REQUIRE(dtype == F32 || dtype == BF16, "gpt2_decode_step: bad dtype %d", dtype);
+    int F = 0;
+    for (int l = 0; l < n_layer; ++l) F = layers[l].ffn > F ? layers[l].ffn : F;
+    PENROZ_REQUIRE(workspace && workspace_bytes >= penroz_gpt2_decode_workspace_bytes(B, C, H, F, pos + 1),
+                   "gpt2_decode_step: workspace too small");
+    const int D = C / H;
+    const size_t es = dtype == F32 ? 4 : 2;
+    uint8_t* w = (uint8_t*)workspace;
+    auto carve = [&](size_t elems) { void* p = w; w += ((elems * es + 255) / 256) * 256; return p; };
+    void* xa = carve((size_t)B * C);
+    void* xb = carve((size_t)B * C);
+    void* ln = carve((size_t)B * C);
+    void* qkv = carve((size_t)B * 3 * C);
+    void* att = carve((size_t)B * C);
+    void* g = carve((size_t)B * F);
+    void* hpre = carve((size_t)B * F);
+    void* attn_scratch = w;
+    const size_t attn_scratch_bytes = penroz_attn_decode_scratch_bytes(B, H, D, pos + 1);
+    int rc = penroz_embed_fwd(tokens, wte, wpe, xa, B, 1, C, V, pos, dtype, dtype, err_flag, stream);
+    if (rc) return rc;
+    void *x = xa, *xo = xb;
+    for (int l = 0; l < n_layer; ++l) {
+        const penroz_gpt2_layer_t& L = layers[l];
+        if ((rc = penroz_layernorm_fwd(x, L.ln1_w, L.ln1_b, ln, nullptr, nullptr, B, C, L.ln1_eps, dtype, dtype, dtype, stream))) return rc;
+        if ((rc = decode_linear(ln, L.qkv_w, L.qkv_b, qkv, nullptr, B, 3 * C, C, 0, 0, dtype, nullptr, stream))) return rc;
+        if ((rc = penroz_kv_append(qkv, L.kv_pool, block_table, max_pages, B, 1, H, D, pos, dtype, stream))) return rc;
+        if ((rc = penroz_attn_decode(qkv, L.kv_pool, block_table, max_pages, att, B, H, D, pos + 1, dtype, attn_scratch, attn_scratch_bytes, stream))) return rc;
+        if ((rc = decode_linear(att, L.proj_w, L.proj_b, xo, x, B, C, C, 2, 0, dtype, nullptr, stream))) return rc;
+        if ((rc = penroz_layernorm_fwd(xo, L.ln2_w, L.ln2_b, ln, nullptr, nullptr, B, C, L.ln2_eps, dtype, dtype, dtype, stream))) return rc;
+        if ((rc = decode_linear(ln, L.fc_w, L.fc_b, g, nullptr, B, L.ffn, C, 1, L.gelu_tanh, dtype, hpre, stream))) return rc;
+        if ((rc = decode_linear(g, L.proj2_w, L.proj2_b, x, xo, B, C, L.ffn, 2, 0, dtype, nullptr, stream))) return rc;
+    }
+    if ((rc = penroz_layernorm_fwd(x, lnf_w, lnf_b, ln, nullptr, nullptr, B, C, lnf_eps, dtype, dtype, dtype, stream))) return rc;
+    if ((rc = decode_linear(ln, head_w, head_b, logits_out, nullptr, B, V, C, 0, 0, dtype, nullptr, stream))) return rc;
+    if (argmax_out) rc = penroz_argmax_rows(logits_out, V, B, V, argmax_out, dtype, stream);
+    return rc;
+}

@@ -147,6 +147,71 @@ class Gpt2Engine:
             return ops.gemm(x2d, w, epilogue=EPI_GELU, bias=b, tanh=tanh)[1]
         return ops.gemm(x2d, w, epilogue=epilogue, bias=b, aux=aux, out_dtype=w.dtype)
 
+    # ------------------------------------------------------------------ native single-token decode step
+    def _native_layers(self, kv):
+        """ctypes array of penroz_gpt2_layer_t for this model and this cache's page pools (built once per cache)."""
+        import ctypes
+        store = kv._paged
+        cached = getattr(store, "native_layers", None)
+        if cached is not None:
+            return cached
+
+        class Layer(ctypes.Structure):
+            _fields_ = [(n, ctypes.c_void_p) for n in ("ln1_w", "ln1_b", "qkv_w", "qkv_b", "proj_w", "proj_b", "ln2_w",
+                                                        "ln2_b", "fc_w", "fc_b", "proj2_w", "proj2_b", "kv_pool")] + \
+                       [("ln1_eps", ctypes.c_float), ("ln2_eps", ctypes.c_float), ("gelu_tanh", ctypes.c_int),
+                        ("ffn", ctypes.c_int)]
+
+        def ptr(p):
+            return None if p is None else p.data_ptr()
+
+        arr = (Layer * self.plan.n_layer)()
+        for i, blk in enumerate(self.plan.blocks):
+            L = arr[i]
+            L.ln1_w, L.ln1_b = ptr(blk.ln1.weight), ptr(blk.ln1.bias)
+            L.qkv_w, L.qkv_b = ptr(blk.qkv.weight), ptr(blk.qkv.bias)
+            L.proj_w, L.proj_b = ptr(blk.proj.weight), ptr(blk.proj.bias)
+            L.ln2_w, L.ln2_b = ptr(blk.ln2.weight), ptr(blk.ln2.bias)
+            L.fc_w, L.fc_b = ptr(blk.fc.weight), ptr(blk.fc.bias)
+            L.proj2_w, L.proj2_b = ptr(blk.proj2.weight), ptr(blk.proj2.bias)
+            L.kv_pool = store.pools[i].data_ptr()
+            L.ln1_eps, L.ln2_eps = blk.ln1.eps, blk.ln2.eps
+            L.gelu_tanh, L.ffn = int(blk.gelu_tanh), blk.fc.out_features
+        store.native_layers = arr
+        return arr
+
+    @torch.no_grad()
+    def decode_step(self, tokens, pos, kv):
+        """One incremental decode step for tokens [B,1] at position `pos` through penroz_gpt2_decode_step (one host
+        call enqueues every kernel of the step). Returns (logits [B,1,V], greedy ids [B,1])."""
+        pl = self.plan
+        B = tokens.shape[0]
+        C, H, V = pl.n_embd, pl.n_head, pl.vocab
+        if pos + 1 > pl.block_size:
+            raise IndexError(f"position {pos + 1} exceeds the position table ({pl.block_size})")
+        store = kv._paged
+        store.ensure_pages(pos + 1)
+        layers = self._native_layers(kv)
+        F = max(b.fc.out_features for b in pl.blocks)
+        need = ops.lib().gpt2_decode_workspace_bytes(B, C, H, F, pl.block_size)
+        ws = getattr(store, "native_ws", None)
+        if ws is None or ws.numel() < need:
+            ws = store.native_ws = torch.empty(need, device=self.device, dtype=torch.uint8)
+        dt = pl.wte.weight.dtype
+        logits = torch.empty((B, 1, V), device=self.device, dtype=dt)
+        ids = torch.empty((B, 1), device=self.device, dtype=torch.int64)
+        self._err_flag.zero_()
+        lnf_b = None if pl.lnf.bias is None else pl.lnf.bias.data_ptr()
+        head_b = None if pl.head.bias is None else pl.head.bias.data_ptr()
+        ops.lib().gpt2_decode_step(tokens.contiguous().data_ptr(), pl.wte.weight.data_ptr(), pl.wpe.weight.data_ptr(),
+                                   layers, pl.n_layer, pl.lnf.weight.data_ptr(), lnf_b, pl.lnf.eps,
+                                   pl.head.weight.data_ptr(), head_b, store.table_dev.data_ptr(), store.max_pages, B, C,
+                                   H, V, pos, ops.dt(pl.wte.weight), ws.data_ptr(), ws.numel(), logits.data_ptr(),
+                                   ids.data_ptr(), self._err_flag.data_ptr(), ops.stream())
+        kv.account_tokens(1, 2 * B * C * logits.element_size(), pl.n_layer)
+        kv.commit(1)
+        return logits, ids
+
     @torch.no_grad()
     def forward_infer(self, idx, targets=None, pos_offset=0, kv=None, last_only=False, collect=False):
         """Forward in the parameter dtype, no autograd. Returns (logits [B,S|1,V], loss|None, activations|None).
