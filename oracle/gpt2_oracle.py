@@ -277,6 +277,36 @@ class Gpt2Oracle:
         self.adamw_step(total, **optim)
         return cost
 
+    @staticmethod
+    def ddp_train_epoch(replicas, loaders, num_steps, batch_size, block_size, **optim):
+        """One epoch of the reference under DistributedDataParallel, all ranks emulated in this process.
+
+        replicas[r] / loaders[r] are rank r's model copy and its loader window (neural_net_model.py:581-594).
+        DDP averages gradients over ranks during backward only while require_backward_grad_sync is set; the reference
+        assigns that flag AFTER forward (neural_net_model.py:647-648), so the value seen by micro-step i's backward
+        is the one written in micro-step i-1: step 0 sees the constructor default True, later steps see False unless
+        num_steps == 1. Each rank then applies AdamW to its own gradient buffer (:664), and the logged
+        cost is the all-reduced mean of the ranks' epoch costs (:667-668, ddp.py:80-85)."""
+        world = len(replicas)
+        totals, costs = [None] * world, [0.0] * world
+        for i in range(num_steps):
+            grads = []
+            for r in range(world):
+                x, y = loaders[r].next_batch()
+                x = np.asarray(x, dtype=np.int64).reshape(batch_size, block_size)
+                y = np.asarray(y, dtype=np.int64).reshape(batch_size, block_size)
+                _, loss = replicas[r].forward(x, y, keep=True)
+                grads.append(replicas[r].backward(1.0 / num_steps))
+                costs[r] += loss / num_steps
+            if i == 0:      # the only micro-step whose backward exchanges gradients
+                mean = {k: sum(g[k] for g in grads) / world for k in grads[0]}
+                grads = [{k: v.copy() for k, v in mean.items()} for _ in range(world)]
+            for r in range(world):
+                totals[r] = grads[r] if totals[r] is None else {k: totals[r][k] + grads[r][k] for k in grads[r]}
+        for r in range(world):
+            replicas[r].adamw_step(totals[r], **optim)
+        return sum(costs) / world
+
     def generate_greedy(self, context, block_size, max_new_tokens, stop_token=None):
         """generate_tokens(temperature=0.0) with the KV cache: prefill, incremental steps, and clear + re-prefill
         once the cache holds block_size tokens (neural_net_model.py:376-389,457-479). Returns row 0."""

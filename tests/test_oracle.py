@@ -78,3 +78,28 @@ def test_loader_windows(golden):
     for rec in ld["offset0"]:
         x, y = lo.next_batch(target_offset=0)
         assert y is None and [int(x[0]), int(x[-1]), int(x.astype(np.int64).sum()), len(x)] == rec
+
+
+@pytest.mark.parametrize("tag,num_steps,epochs", [("ns1", 1, 10), ("ns2", 2, 6)])
+def test_two_rank_ddp_epochs(golden, tag, num_steps, epochs):
+    """The oracle's in-process DDP emulation against the reference run under 2-rank gloo DDP
+    (tests/golden/make_golden_ddp.py): plain DDP, and accumulation where only micro-step 0 exchanges gradients
+    and the two ranks' weights drift apart."""
+    import os
+    g, _ = golden
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_ddp.npz"))
+    shard = np.random.default_rng(1234).integers(0, 65, size=2 ** 17).astype(np.uint16)
+    micro = 16          # every micro-step reads a full batch_size x block_size buffer (neural_net_model.py:629-631);
+    buf = micro * 64    # step_size only sets num_steps (:581)
+    reps = [Gpt2Oracle(_state(g, "tiny/init/"), 2, 4) for _ in range(2)]
+    lds = [LoaderOracle([shard], 0, buf * r, buf, buf * 2) for r in range(2)]
+    costs = [Gpt2Oracle.ddp_train_epoch(reps, lds, num_steps, micro, 64) for _ in range(epochs)]
+    np.testing.assert_allclose(costs, d[f"{tag}/r0/cost"], rtol=2e-5)
+    for r in range(2):
+        pre = f"{tag}/r{r}/final/"
+        for k in [k for k in d.files if k.startswith(pre)]:
+            assert np.abs(reps[r].p[k[len(pre):]] - d[k]).max() < 1e-4, k
+    w0, w1 = d[f"{tag}/r0/final/layers.5.weight"], d[f"{tag}/r1/final/layers.5.weight"]
+    assert np.array_equal(w0, w1) == (num_steps == 1)
+    same = np.array_equal(reps[0].p["layers.5.weight"], reps[1].p["layers.5.weight"])
+    assert same == (num_steps == 1)
