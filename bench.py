@@ -433,7 +433,23 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def _reserve_stdout():
+    """The contract is ONE JSON line on stdout. Libraries (NCCL's version banner, torch-elastic notices) also write to
+    file descriptor 1, so keep a private duplicate of it for the result line and point fd 1 at stderr."""
+    global print
+    sys.stdout.flush()
+    keep = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    builtin_print = print
+
+    def print(*a, **kw):        # noqa: A001 - module-local: every print() in this file is a result line
+        kw.setdefault("file", keep)
+        kw.setdefault("flush", True)
+        builtin_print(*a, **kw)
+
+
 def main():
+    _reserve_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

@@ -291,6 +291,26 @@ __device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const void* 
 __device__ __forceinline__ void mbar_arrive_on_leader(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerMask) : "memory");
 }
+// ---- handing a word to the peer CTA of a pair: st.async writes it into the peer's shared memory and completes 4
+// transaction bytes on the peer's mbarrier, so the reader needs nothing stronger than its usual CTA-scope wait.
+// (A release.cluster arrive would cost a MEMBAR.GPU per hand-off, an acquire.cluster wait an L1 invalidate.)
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_async_s32(uint32_t cluster_addr, int v, uint32_t cluster_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];"
+                 ::"r"(cluster_addr), "r"(v), "r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ int ld_shared_s32(uint32_t saddr) {
+    int v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_shared_s32(uint32_t saddr, int v) {
+    asm volatile("st.shared.s32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+}
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_result, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result), "r"(ncols) : "memory");
 }

@@ -48,7 +48,79 @@ struct GemmParams {
     long long ldaux;
     int gelu_tanh;
     int beta;
+    int feed_slot;   // which g_feed counter pair this launch draws its work units from
 };
+
+// ------------------------------------------------------------------ dynamic tile feed
+// A persistent grid with a fixed round-robin schedule assumes it owns every SM for its whole duration. It does not:
+// the gradient all-reduce (NCCL, on a side stream) takes SMs away while backward GEMMs run, and a CTA that cannot
+// become resident leaves its whole share of tiles waiting until another CTA has finished ITS share -- the kernel
+// then takes up to twice as long. Here every work unit, the first included, is drawn from a global counter by the
+// CTA's (or CTA pair's) TMA producer, one unit ahead of use so the atomic's latency hides behind a tile's loads;
+// a late CTA finds the counter exhausted and exits. The producer hands unit ids to the MMA and epilogue warps (and,
+// in the pair kernel, to the odd CTA through distributed shared memory) over a small ring guarded by mbarriers.
+// Counters live in a file-scope device array, one pair per launch in flight (the host deals them out round robin);
+// the last CTA to leave resets its pair, so no launch ever needs a memset.
+constexpr int kFeedSlots = 6;        // ring depth: ids are published a tile ahead of a producer that itself runs
+                                     // up to ~2 tiles ahead of the epilogue
+constexpr int kFeedCounters = 1024;
+__device__ unsigned int g_feed[kFeedCounters][2];   // {next unit, CTAs done}
+
+// ring layout at `base` (120 bytes): full[6] mbarriers | empty[6] mbarriers | unit id[6]
+constexpr uint32_t kFeedOffset = 136u;   // behind the pipeline barriers (<= 128 B) and the TMEM pointer, inside 256 B
+static_assert(kFeedOffset + 20u * kFeedSlots <= 256u, "tile-feed ring must fit the 256-byte barrier area");
+__device__ __forceinline__ uint32_t feed_full(uint32_t base, int s) { return base + 8u * s; }
+__device__ __forceinline__ uint32_t feed_empty(uint32_t base, int s) { return base + 8u * kFeedSlots + 8u * s; }
+__device__ __forceinline__ uint32_t feed_unit(uint32_t base, int s) { return base + 16u * kFeedSlots + 4u * s; }
+
+// Producer side, one lane: publish `u` (-1 = no more work) in ring slot `s`. PAIR: also into the odd CTA's ring.
+template <bool PAIR>
+__device__ __forceinline__ void feed_publish(uint32_t base, int s, uint32_t ph, int u) {
+    mbar_wait(feed_empty(base, s), ph ^ 1u);
+    st_shared_s32(feed_unit(base, s), u);
+    mbar_arrive(feed_full(base, s));
+    if (PAIR) st_async_s32(mapa_rank(feed_unit(base, s), 1), u, mapa_rank(feed_full(base, s), 1));
+}
+
+// Consumer side: a warp-uniform cursor over the ring. next() returns the unit id, or -1 when the feed is exhausted.
+// In the odd CTA of a pair (`odd`) the slot's "empty" arrival goes to the even CTA's barrier, which the publisher
+// waits on; the shuffle between the read and that arrival keeps the read ahead of any overwrite. One reader per odd
+// CTA (`rearm`, its producer warp) re-arms each full barrier for the next st.async as soon as it has seen the
+// current phase complete.
+template <bool PAIR>
+struct FeedCursor {
+    uint32_t base;
+    int s;
+    uint32_t ph;
+    bool odd, rearm;
+    __device__ __forceinline__ explicit FeedCursor(uint32_t b, bool odd_cta = false, bool rearm_full = false)
+        : base(b), s(0), ph(0), odd(odd_cta), rearm(rearm_full) {}
+    __device__ __forceinline__ int next(int lane) {
+        int u = 0;
+        if (lane == 0) {
+            mbar_wait(feed_full(base, s), ph);
+            u = ld_shared_s32(feed_unit(base, s));
+            if (PAIR && rearm) mbar_expect_tx(feed_full(base, s), 4);
+        }
+        u = __shfl_sync(0xffffffffu, u, 0);
+        if (lane == 0) {
+            if (PAIR && odd) mbar_arrive_on_leader(feed_empty(base, s)); else mbar_arrive(feed_empty(base, s));
+        }
+        if (++s == kFeedSlots) { s = 0; ph ^= 1u; }
+        return u;
+    }
+};
+
+// Called by a drawing thread right after the draw that came back exhausted (its last): the last of the launch's
+// `drawers` to get here resets the counters for the slot's next user. Nobody draws after its own exhausted draw, so
+// the reset races with nothing, and it sits behind the CTA's remaining tiles instead of at the kernel's tail.
+__device__ __forceinline__ void feed_retire(int slot, unsigned int drawers) {
+    const unsigned int done = atomicAdd(&g_feed[slot][1], 1u);
+    if (done == drawers - 1) {
+        g_feed[slot][0] = 0u;
+        g_feed[slot][1] = 0u;
+    }
+}
 
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_enc, uint32_t sbo_enc) {
     // cute::UMMA::SmemDescriptor: start[0,14) | LBO[16,30) | SBO[32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
@@ -320,11 +392,14 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + s); };
     auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + 2 + s); };
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
+    const uint32_t feed = bar_base + kFeedOffset;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
+    unsigned int first_unit = 0;
     if (warp == 0 && lane == 0) {
+        first_unit = atomicAdd(&g_feed[p.feed_slot][0], 1u);   // in flight while the CTA sets itself up
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
     }
@@ -336,6 +411,10 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
             mbar_init(tempty_bar(s), 8);
+        }
+        for (int s = 0; s < kFeedSlots; ++s) {
+            mbar_init(feed_full(feed, s), 1);
+            mbar_init(feed_empty(feed, s), 1 + 8);   // MMA warp + 8 epilogue warps
         }
         mbar_fence_init();
     }
@@ -352,9 +431,20 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer
-        int s = 0;
-        uint32_t ph = 0;
-        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        int s = 0, fs = 0;
+        uint32_t ph = 0, fph = 0;
+        // Unit ids are published one tile ahead: the next unit is drawn when a tile's loads start and handed to the
+        // other warps after its second k-block has been issued, by which time the atomic has long returned.
+        int u = __shfl_sync(0xffffffffu, (int)first_unit, 0);
+        bool live = (unsigned)u < (unsigned)units;
+        if (lane == 0) {
+            feed_publish<false>(feed, fs, fph, live ? u : -1);
+            if (!live) feed_retire(p.feed_slot, gridDim.x);
+        }
+        if (++fs == kFeedSlots) { fs = 0; fph ^= 1u; }
+        while (live) {
+            int drawn = 0;
+            if (lane == 0) drawn = (int)atomicAdd(&g_feed[p.feed_slot][0], 1u);
             const int tile = u % (p.tiles_m * p.tiles_n);
             const int split = u / (p.tiles_m * p.tiles_n);
             const int m0 = (tile / p.tiles_n) * BM;
@@ -382,10 +472,18 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         for (int j = 0; j < BN / 64; ++j)
                             tma_load_2d(sB + j * 8192, &tmB, full_bar(s), n0 + 64 * j, k0);
                     }
+                    if (kb == min(1, nkb - 1)) {
+                        const bool more = (unsigned)drawn < (unsigned)units;
+                        feed_publish<false>(feed, fs, fph, more ? drawn : -1);
+                        if (!more) feed_retire(p.feed_slot, gridDim.x);
+                    }
                 }
                 __syncwarp();
                 if (++s == Cfg::kStages) { s = 0; ph ^= 1u; }
             }
+            if (++fs == kFeedSlots) { fs = 0; fph ^= 1u; }
+            u = __shfl_sync(0xffffffffu, drawn, 0);
+            live = (unsigned)u < (unsigned)units;
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
@@ -400,7 +498,8 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         constexpr uint32_t kDescHi = desc_hi(64u);   // SBO = 1024 B for both majors
         int s = 0, as = 0;
         uint32_t ph = 0, aph = 0;
-        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        FeedCursor<false> cur(feed);
+        for (int u = cur.next(lane); u >= 0; u = cur.next(lane)) {
             const int split = u / (p.tiles_m * p.tiles_n);
             const int kb0 = split * p.kb_per_split;
             const int nkb = min(p.kb_per_split, p.kb_total - kb0);
@@ -439,7 +538,8 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         float* stg = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256) + (warp - 4) * (32 * 33);
         int as = 0;
         uint32_t aph = 0;
-        for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        FeedCursor<false> cur(feed);
+        for (int u = cur.next(lane); u >= 0; u = cur.next(lane)) {
             const int tile = u % (p.tiles_m * p.tiles_n);
             const int m0 = (tile / p.tiles_n) * BM;
             const int n0 = (tile % p.tiles_n) * BN;
@@ -531,8 +631,11 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = (rank == 0);
+    const uint32_t feed = bar_base + kFeedOffset;   // tile-feed ring; the leader's producer fills both CTAs' copies
 
+    unsigned int first_unit = 0;
     if (warp == 0 && lane == 0) {
+        if (leader) first_unit = atomicAdd(&g_feed[p.feed_slot][0], 1u);
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
     }
@@ -545,6 +648,13 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             mbar_init(tfull_bar(s), 1);    // one multicast commit
             mbar_init(tempty_bar(s), 2 * EW);  // every epilogue warp of both CTAs (only the leader's copy is used)
         }
+        for (int s = 0; s < kFeedSlots; ++s) {
+            mbar_init(feed_full(feed, s), 1);
+            // readers: the leader's MMA warp, the odd CTA's producer, every epilogue warp of both CTAs
+            // (only the leader's copy of the empty barriers is used)
+            mbar_init(feed_empty(feed, s), 2 + 2 * EW);
+            if (!leader) mbar_expect_tx(feed_full(feed, s), 4);   // armed for the leader's first st.async
+        }
         mbar_fence_init();
     }
     if (warp == 2) {
@@ -556,15 +666,30 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
 
-    const int n_clusters = gridDim.x >> 1;
-    const int cid = blockIdx.x >> 1;
     const int units = p.tiles_m * p.tiles_n * p.splits;   // tiles_m counts 256-row tiles here
 
     if (warp == 0) {
-        // ------------------------------------------------------------ TMA producer (both CTAs)
-        int s = 0;
-        uint32_t ph = 0;
-        for (int u = cid; u < units; u += n_clusters) {
+        // ------------------------------------------------------------ TMA producer (both CTAs); the leader's also
+        // draws the pair's work units and publishes them to both CTAs
+        int s = 0, fs = 0;
+        uint32_t ph = 0, fph = 0;
+        // (published one tile ahead, so the odd CTA's producer never waits for the hop through DSMEM)
+        FeedCursor<true> cur(feed, !leader, !leader);
+        int u;
+        if (leader) {
+            u = __shfl_sync(0xffffffffu, (int)first_unit, 0);
+            if ((unsigned)u >= (unsigned)units) u = -1;
+            if (lane == 0) {
+                feed_publish<true>(feed, fs, fph, u);
+                if (u < 0) feed_retire(p.feed_slot, gridDim.x >> 1);
+            }
+            if (++fs == kFeedSlots) { fs = 0; fph ^= 1u; }
+        } else {
+            u = cur.next(lane);
+        }
+        while (u >= 0) {
+            int drawn = 0;
+            if (leader && lane == 0) drawn = (int)atomicAdd(&g_feed[p.feed_slot][0], 1u);
             const int tile = u % (p.tiles_m * p.tiles_n);
             const int split = u / (p.tiles_m * p.tiles_n);
             const int m0 = (tile / p.tiles_n) * (2 * BM) + (int)rank * BM;
@@ -590,9 +715,21 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll
                         for (int j = 0; j < BN / 128; ++j) tma_load_2d_pair(sB + j * 8192, &tmB, full_bar(s), n0 + 64 * j, k0);
                     }
+                    if (leader && kb == min(1, nkb - 1)) {
+                        const bool more = (unsigned)drawn < (unsigned)units;
+                        feed_publish<true>(feed, fs, fph, more ? drawn : -1);
+                        if (!more) feed_retire(p.feed_slot, gridDim.x >> 1);
+                    }
                 }
                 __syncwarp();
                 if (++s == Cfg::kStages) { s = 0; ph ^= 1u; }
+            }
+            if (leader) {
+                if (++fs == kFeedSlots) { fs = 0; fph ^= 1u; }
+                u = __shfl_sync(0xffffffffu, drawn, 0);
+                if ((unsigned)u >= (unsigned)units) u = -1;
+            } else {
+                u = cur.next(lane);
             }
         }
     } else if (warp == 1) {
@@ -605,7 +742,8 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             constexpr uint32_t kDescHi = desc_hi(64u);
             int s = 0, as = 0;
             uint32_t ph = 0, aph = 0;
-            for (int u = cid; u < units; u += n_clusters) {
+            FeedCursor<true> cur(feed);
+            for (int u = cur.next(lane); u >= 0; u = cur.next(lane)) {
                 const int split = u / (p.tiles_m * p.tiles_n);
                 const int kb0 = split * p.kb_per_split;
                 const int nkb = min(p.kb_per_split, p.kb_total - kb0);
@@ -642,7 +780,8 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         float* stg = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256) + (warp - 4) * (32 * 33);
         int as = 0;
         uint32_t aph = 0;
-        for (int u = cid; u < units; u += n_clusters) {
+        FeedCursor<true> cur(feed, !leader);
+        for (int u = cur.next(lane); u >= 0; u = cur.next(lane)) {
             const int tile = u % (p.tiles_m * p.tiles_n);
             const int m0 = (tile / p.tiles_n) * (2 * BM) + (int)rank * BM;
             const int n0 = (tile % p.tiles_n) * BN;
@@ -823,6 +962,8 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2; p.aux = aux; p.ldaux = ldaux;
     p.gelu_tanh = (flags & 1) ? 1 : 0;
     p.beta = (flags & 2) ? 1 : 0;
+    static std::atomic<unsigned int> feed_seq{0};
+    p.feed_slot = (int)(feed_seq.fetch_add(1, std::memory_order_relaxed) % kFeedCounters);
 
     const int sms = num_sms();
     const int tiles_m = (M + BM - 1) / BM;

@@ -494,8 +494,17 @@ class Gpt2Engine:
         """One AdamW update over the flat buffers with the hyper-parameters of the (stock) torch optimizer's single
         param group; also refreshes the bf16 shadow weights in the same pass."""
         fl = self.flat
-        if self.grad_sync is not None:
-            self.grad_sync.wait_all()
+        gs = self.grad_sync
+        # With every bucket still in flight (the usual one-micro-step epoch) the update runs bucket by bucket in
+        # arrival order, so AdamW on the early buckets hides the all-reduce of the last ones (the embeddings, whose
+        # gradient only exists once backward has finished). AdamW is elementwise, so the result is unchanged.
+        # Clipping needs the norm of the whole reduced gradient first.
+        ranges = None
+        if gs is not None:
+            if self.clip_grad_norm <= 0.0 and gs.covers_all and gs.all_in_flight():
+                ranges = gs.drain()
+            else:
+                gs.wait_all()
         grp = self.optimizer.param_groups[0]
         if len(self.optimizer.param_groups) != 1:
             raise PenrozError("fused AdamW expects the reference's single parameter group (mappers.py:267-274)")
@@ -507,7 +516,9 @@ class Gpt2Engine:
             norm = self._buf("gnorm", (1,), torch.float32)
             mult = self._buf("gmult", (1,), torch.float32)
             ops.grad_norm(fl.g, self.clip_grad_norm, norm, mult)
-        ops.adamw_flat(fl.p, fl.g, fl.m, fl.v, fl.shadow if self.mode == "amp" else None, lr=grp["lr"],
-                       betas=grp["betas"], eps=grp["eps"], weight_decay=grp["weight_decay"], step=self.step_count,
-                       grad_mult=mult, zero_grad=False)
+        shadow = fl.shadow if self.mode == "amp" else None
+        for lo, hi in (ranges if ranges is not None else [(0, fl.p.numel())]):
+            ops.adamw_flat(fl.p[lo:hi], fl.g[lo:hi], fl.m[lo:hi], fl.v[lo:hi], None if shadow is None else shadow[lo:hi],
+                           lr=grp["lr"], betas=grp["betas"], eps=grp["eps"], weight_decay=grp["weight_decay"],
+                           step=self.step_count, grad_mult=mult, zero_grad=False)
         fl.step_tensor.fill_(float(self.step_count))

@@ -49,6 +49,10 @@ class GradSync:
             cur_names.append(name)
         flush()
         self._pending = []
+        spans = sorted((lo, hi) for lo, hi, _ in self.buckets)
+        # True when the buckets tile the whole flat buffer, so a per-bucket optimizer pass touches every element once
+        self.covers_all = bool(spans) and spans[0][0] == 0 and spans[-1][1] == flat_grad.numel() and all(
+            a[1] == b[0] for a, b in zip(spans, spans[1:]))
         self._cuda = flat_grad.is_cuda
         self._stream = torch.cuda.Stream(device=flat_grad.device) if self._cuda else None
         self.launched = []         # bucket indices in launch order (inspected by tests)
@@ -70,9 +74,9 @@ class GradSync:
             with torch.cuda.stream(self._stream):
                 self._stream.wait_event(ev)
                 work = self._reduce(view)
-            self._pending.append((work, view))
+            self._pending.append((work, view, lo, hi))
         else:
-            self._pending.append((self._reduce(view), view))
+            self._pending.append((self._reduce(view), view, lo, hi))
 
     def _reduce(self, view):
         if self.backend == "nccl":
@@ -81,12 +85,24 @@ class GradSync:
 
     def wait_all(self):
         """Make the compute stream (or the host, for Gloo) wait for every launched bucket."""
-        for work, view in self._pending:
+        for _ in self.drain():
+            pass
+
+    def all_in_flight(self) -> bool:
+        """Every bucket has been launched and none has been waited for yet."""
+        return len(self._pending) == len(self.buckets) and len(set(self.launched)) == len(self.buckets)
+
+    def drain(self):
+        """Yield (lo, hi) for each launched bucket in launch order, right after making the compute stream (or the
+        host, for Gloo) wait for THAT bucket only: the caller can update a reduced bucket's parameters while the
+        later buckets are still on the wire."""
+        pending, self._pending = self._pending, []
+        self.launched.clear()
+        for work, view, lo, hi in pending:
             work.wait()
             if self.backend != "nccl":
                 view.div_(self.world)
-        self._pending.clear()
-        self.launched.clear()
+            yield lo, hi
 
 
 def gpt2_segments(flat, plan) -> list:

@@ -1,6 +1,8 @@
 # quick perf probe of the fused step at the headline shape (not the bench; just to see where time goes)
 import sys, os, time, torch
 sys.path.insert(0, "tests"); sys.path.insert(0, "penr-oz-neural-network-v3-torch-ddp_b200")
+import penroz._lib as _L
+if os.environ.get("PENROZ_AB_LIB"): _L.LIB_PATH = os.path.abspath(os.environ["PENROZ_AB_LIB"])   # A/B against another build
 from helpers import build_gpt, scratch_cwd
 root=os.getcwd(); scratch_cwd()
 B=int(os.environ.get("PB","32")); T=1024

@@ -155,7 +155,17 @@ def _sync_worker(rank, world, port, out_dir):
         gs.ready(name)
         order = list(gs.launched)
     gs.wait_all()
-    torch.save({"p": fl.p.clone(), "g": fl.g.clone(), "order": order, "buckets": gs.buckets,
+    g_all = fl.g.clone()
+    # second round, drained bucket by bucket: a bucket is final when drain() yields it, whatever the later ones do
+    fl.g.copy_(torch.arange(fl.total, dtype=torch.float32) * (rank + 1))
+    for name, _, _ in segs:
+        gs.ready(name)
+    in_flight = gs.all_in_flight()
+    drained = []
+    for lo, hi in gs.drain():
+        drained.append((lo, hi, bool(torch.equal(fl.g[lo:hi], torch.arange(lo, hi, dtype=torch.float32) * 1.5))))
+    torch.save({"p": fl.p.clone(), "g": g_all, "order": order, "buckets": gs.buckets, "covers_all": gs.covers_all,
+                "in_flight": in_flight, "after": gs.all_in_flight(), "drained": drained,
                 "segs": segs, "total": fl.total}, os.path.join(out_dir, f"r{rank}.pt"))
     dist.destroy_process_group()
 
@@ -179,6 +189,9 @@ def test_bucketed_gradient_sync_world_size_2_gloo(tmp_path):
     assert r0["order"] == list(range(len(r0["buckets"])))  # buckets go out in backward-completion order
     assert r0["segs"][0][0] == "head" and r0["segs"][-1][0] == "embed"
     assert 1 < len(r0["buckets"]) < len(r0["segs"]) + 1    # small adjacent stages were merged
+    assert r0["covers_all"] and r0["in_flight"] and not r0["after"]
+    assert [(lo, hi) for lo, hi, _ in r0["drained"]] == [(lo, hi) for lo, hi, _ in r0["buckets"]]
+    assert all(ok for _, _, ok in r0["drained"]) and all(ok for _, _, ok in r1["drained"])
 
 
 def test_kv_cache_api_dense_store():
