@@ -281,7 +281,8 @@ class NeuralNetworkModel(nn.Module):
     @torch.no_grad()
     def compute_output(self, input_data: list, target: list | int | None = None) -> Tuple[list, float]:
         """Activated output of the last layer and, with a target, the cost — no training (/output/)."""
-        self.eval()
+        if self.training or any(m.training for m in self.modules()):    # eval() walks ~170 modules: skip when already there
+            self.eval()
         self.layers.training = False
         self._maybe_accelerate()
         first_param = next(self.parameters())
@@ -300,7 +301,8 @@ class NeuralNetworkModel(nn.Module):
     def evaluate_model(self, dataset_id: str, target_dataset_id: str | None, shard: int,
                        epochs: int, batch_size: int, block_size: int, step_size: int) -> float:
         """Average cost over `epochs` loader windows (each re-used for every step), no training (/evaluate/)."""
-        self.eval()
+        if self.training or any(m.training for m in self.modules()):    # eval() walks ~170 modules: skip when already there
+            self.eval()
         self.layers.training = False
         self._maybe_accelerate()
         window = batch_size * block_size
@@ -336,10 +338,16 @@ class NeuralNetworkModel(nn.Module):
 
     # ------------------------------------------------------------------ generation
     def _find_attention_layers(self) -> list[CausalSelfAttention]:
-        return [m for m in self.modules() if isinstance(m, CausalSelfAttention)]
+        found = self.__dict__.get("_attention_layers")       # the module tree is fixed once the model is built
+        if found is None:
+            found = self.__dict__["_attention_layers"] = [m for m in self.modules() if isinstance(m, CausalSelfAttention)]
+        return found
 
     def _find_position_embeddings(self) -> list[PositionEmbedding]:
-        return [m for m in self.modules() if isinstance(m, PositionEmbedding)]
+        found = self.__dict__.get("_position_layers")
+        if found is None:
+            found = self.__dict__["_position_layers"] = [m for m in self.modules() if isinstance(m, PositionEmbedding)]
+        return found
 
     def _attach_kv_cache(self) -> tuple[KVCache | None, list[PositionEmbedding]]:
         """Create one KV cache for all attention layers and attach it; returns (cache, position embeddings)."""
@@ -360,7 +368,8 @@ class NeuralNetworkModel(nn.Module):
 
     def _prepare_generation(self, input_context: list, max_new_tokens: int, temperature: float, top_k: int | None):
         """eval mode, context tensor on the parameter device, and the softmax used for sampling."""
-        self.eval()
+        if self.training or any(m.training for m in self.modules()):    # eval() walks ~170 modules: skip when already there
+            self.eval()
         self.layers.training = False
         self._maybe_accelerate()
         first_param = next(self.parameters())

@@ -341,10 +341,21 @@ static int decode_linear(const void* x, const void* W, const void* b, void* out,
 }
 }  // namespace penroz
 
+namespace penroz {   // decode_fused.cu: the five-launches-per-block step for B <= 8
+bool decode_small_supported(int B, int C, int H, int dtype);
+size_t decode_small_extra_bytes(int B);
+int decode_step_small(const long long* tokens, const void* wte, const void* wpe, const penroz_gpt2_layer_t* layers,
+                      int n_layer, const void* lnf_w, const void* lnf_b, float lnf_eps, const void* head_w,
+                      const void* head_b, const int* block_table, int max_pages, int B, int C, int H, int V, int pos,
+                      int dtype, void* xa, void* xb, void* qkv, void* att, void* g, float* part, void* extra,
+                      void* logits_out, long long* argmax_out, int* err_flag, cudaStream_t st);
+}
+
 extern "C" size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F, int t_len_max) {
     const size_t es = 4;  // sized for fp32; bf16 uses half of the activation part
-    const size_t act = (size_t)B * ((size_t)2 * C + C + 3 * C + C + 2 * (size_t)F + C) * es;
-    return act + penroz_attn_decode_scratch_bytes(B, H, C / H, t_len_max) + 256;
+    const size_t act = (size_t)B * ((size_t)2 * C + C + 3 * C + C + 2 * (size_t)F + C) * es + 8 * 256;
+    return act + penroz_attn_decode_scratch_bytes(B, H, C / H, t_len_max) + 256 +
+           (B <= 8 ? decode_small_extra_bytes(B) : 0);
 }
 
 extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte, const void* wpe,
@@ -373,6 +384,12 @@ extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte,
     void* hpre = carve((size_t)B * F);
     void* attn_scratch = w;
     const size_t attn_scratch_bytes = penroz_attn_decode_scratch_bytes(B, H, D, pos + 1);
+    if (decode_small_supported(B, C, H, dtype) && !getenv("PENROZ_DECODE_UNFUSED")) {
+        void* extra = w + ((attn_scratch_bytes + 255) / 256) * 256;
+        return decode_step_small(tokens, wte, wpe, layers, n_layer, lnf_w, lnf_b, lnf_eps, head_w, head_b, block_table,
+                                 max_pages, B, C, H, V, pos, dtype, xa, xb, qkv, att, g, (float*)attn_scratch, extra,
+                                 logits_out, argmax_out, err_flag, (cudaStream_t)stream);
+    }
     int rc = penroz_embed_fwd(tokens, wte, wpe, xa, B, 1, C, V, pos, dtype, dtype, err_flag, stream);
     if (rc) return rc;
     void *x = xa, *xo = xb;
