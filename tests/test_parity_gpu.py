@@ -189,3 +189,56 @@ def test_other_baseline_layouts_bf16_tracks_fp32(env, name, L, H, C):
     assert all(np.isfinite(losses[True])) and losses[False][2] < losses[False][0]
     assert abs(losses[True][0] - losses[False][0]) < 2e-2, losses
     assert abs(losses[True][2] - losses[False][2]) < 5e-2, losses
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B", [1, 3, 8])
+def test_fused_small_batch_decode_step_matches_unfused(env, monkeypatch, dtype, B):
+    """The five-launch token step (decode_fused.cu: LayerNorm / residual / GELU / page scatter fused into the GEMVs,
+    cluster-merged attention, arg-max candidates from the LM head) against the one-kernel-per-op step on the 124M
+    layout: same logits up to summation order, same K/V pages, same greedy ids."""
+    from kv_cache import KVCache
+    m = build_gpt(f"dec124_{B}_{dtype}".replace(".", "_"), 2, 12, 768, 1024, 50257)
+    if dtype != torch.float32:
+        m.to(dtype=dtype)
+    m.to("cuda")
+    eng = m._engine()
+    pl = m._plan
+    gen = torch.Generator().manual_seed(B)
+    prompt = torch.randint(0, 50257, (B, 70), generator=gen).to(env)       # 70 tokens: spills into a second page
+    nxt = torch.randint(0, 50257, (4, B, 1), generator=gen).to(env)
+
+    def run(unfused):
+        if unfused:
+            monkeypatch.setenv("PENROZ_DECODE_UNFUSED", "1")
+        else:
+            monkeypatch.delenv("PENROZ_DECODE_UNFUSED", raising=False)
+        kv = KVCache(pl.n_layer)
+        kv.paged(B, pl.n_head, pl.head_dim, pl.wte.weight.dtype, env, capacity_hint=1024)
+        with torch.inference_mode():
+            eng.forward_infer(prompt, None, pos_offset=0, kv=kv, last_only=True)
+            outs = []
+            for i in range(4):
+                logits, ids = eng.decode_step(nxt[i], 70 + i, kv)
+                outs.append((logits.float().clone(), ids.clone()))
+        return outs, kv
+    fused, kv_f = run(False)
+    plain, kv_p = run(True)
+    tol = 2e-4 if dtype == torch.float32 else 6e-2
+    for (lf, idf), (lp, idp) in zip(fused, plain):
+        assert lf.shape == (B, 1, 50257)
+        assert (lf - lp).abs().max().item() <= tol * max(1.0, lp.abs().max().item())
+        top2 = lp.view(B, -1).topk(2, dim=-1).values
+        clear = (top2[:, 0] - top2[:, 1]) > 4 * tol * max(1.0, lp.abs().max().item())
+        assert torch.equal(idf.view(-1)[clear], idp.view(-1)[clear])
+        assert torch.equal(idf.view(-1), lf.view(B, -1).argmax(dim=-1))      # arg-max candidates == arg-max of its own logits
+    assert kv_f.seq_len() == kv_p.seq_len() == 74
+    sf, sp = kv_f._paged, kv_p._paged
+    assert torch.equal(sf.table_host, sp.table_host)
+    for layer in range(pl.n_layer):
+        for b in range(B):
+            for pg, used in ((0, 64), (1, 10)):              # 74 cached positions: one full page and ten slots
+                page = int(sf.table_host[b, pg])
+                kf = sf.pools[layer][page, :, :, :used].float()
+                kp = sp.pools[layer][page, :, :, :used].float()
+                assert (kf - kp).abs().max().item() <= tol * max(1.0, kp.abs().max().item())
