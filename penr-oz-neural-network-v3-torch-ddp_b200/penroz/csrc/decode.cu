@@ -341,7 +341,7 @@ static int decode_linear(const void* x, const void* W, const void* b, void* out,
 }
 }  // namespace penroz
 
-namespace penroz {   // decode_fused.cu: the five-launches-per-block step for B <= 8
+namespace penroz {   // decode_fused.cu: the five-launches-per-block step for small batches
 bool decode_small_supported(int B, int C, int H, int dtype);
 size_t decode_small_extra_bytes(int B);
 int decode_step_small(const long long* tokens, const void* wte, const void* wpe, const penroz_gpt2_layer_t* layers,
@@ -355,7 +355,7 @@ extern "C" size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F,
     const size_t es = 4;  // sized for fp32; bf16 uses half of the activation part
     const size_t act = (size_t)B * ((size_t)2 * C + C + 3 * C + C + 2 * (size_t)F + C) * es + 8 * 256;
     return act + penroz_attn_decode_scratch_bytes(B, H, C / H, t_len_max) + 256 +
-           (B <= 8 ? decode_small_extra_bytes(B) : 0);
+           decode_small_extra_bytes(B);
 }
 
 extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte, const void* wpe,

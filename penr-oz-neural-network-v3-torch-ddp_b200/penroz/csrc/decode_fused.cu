@@ -1,4 +1,4 @@
-// Small-batch (B <= 8) single-token step: five launches per transformer block instead of nine, every one a
+// Small-batch (B <= 16) single-token step: five launches per transformer block instead of nine, every one a
 // weight-streaming kernel sized for HBM latency rather than for FLOPs.
 //
 // At B = 1 a GPT-2 124M token reads 326 MB of weights (51 us at the measured 6.4 TB/s) but each Linear is only
@@ -72,6 +72,16 @@ gemv_kernel(const GemvParams p, int rpb) {
                 prefetch_l2(reinterpret_cast<const char*>(W + (size_t)(nbp + r) * p.ldw) + (size_t)c * 128);
             }
     }
+    // LayerNorm's gamma / beta are constants too: one 16-byte slice per thread, fetched while the producer still runs
+    constexpr int VNP = Vec16<T>::N;
+    Vec16<T> g_pre, b_pre;
+    const bool ln_pre = (PRO == PRO_LN) && (K % VNP == 0) && (K / VNP <= 128) &&
+                        ((reinterpret_cast<uintptr_t>(p.ln_w) & 15) == 0) &&
+                        (!p.ln_b || (reinterpret_cast<uintptr_t>(p.ln_b) & 15) == 0);
+    if (ln_pre && tid < K / VNP) {
+        g_pre.load(reinterpret_cast<const T*>(p.ln_w) + tid * VNP);
+        if (p.ln_b) b_pre.load(reinterpret_cast<const T*>(p.ln_b) + tid * VNP);
+    }
     pdl_wait();
     // ---- prologue: activation rows -> xs. All global loads of all rows are issued before anything waits on them.
     {
@@ -126,8 +136,12 @@ gemv_kernel(const GemvParams p, int rpb) {
 #pragma unroll 2
             for (int c = tid; c < kv; c += 128) {
                 Vec16<T> gv, bv;
-                gv.load(gw + c * VNX);
-                if (gb) bv.load(gb + c * VNX);
+                if (ln_pre) {
+                    gv = g_pre; bv = b_pre;
+                } else {
+                    gv.load(gw + c * VNX);
+                    if (gb) bv.load(gb + c * VNX);
+                }
                 for (int r = 0; r < mrows; ++r) {
                     float* d = xs + r * K + c * VNX;
                     const float mean = st_mean[r], rstd = st_rstd[r];
@@ -562,9 +576,13 @@ static int fused_splits(int B, int H, int t_len) {
     return want < 1 ? 1 : want;
 }
 
-// B <= 8 and a head dimension the lane layout of attn_decode_split2_kernel covers
+// small batch (measured: faster than the tensor-core path up to B = 16, slower at 64) and a head dimension the lane layout of attn_decode_split2_kernel covers
+static int small_batch_limit() {   // PENROZ_DECODE_SMALL_MAX overrides the largest batch the fused step takes
+    static const int v = getenv("PENROZ_DECODE_SMALL_MAX") ? atoi(getenv("PENROZ_DECODE_SMALL_MAX")) : 16;
+    return v;
+}
 bool decode_small_supported(int B, int C, int H, int dtype) {
-    if (B > 8 || C % H) return false;
+    if (B > small_batch_limit() || C % H) return false;
     const int D = C / H, vn = (dtype == F32) ? 4 : 8;
     if (D % vn) return false;
     const int lpk = D / vn;
