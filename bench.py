@@ -51,7 +51,7 @@ def measured_peaks():
 
 def ncu_traffic_per_launch(family: str):
     """Mean DRAM bytes per launch of a kernel family, from the committed ncu launch list of this same command."""
-    path = os.path.join(ROOT, "profiles", "r01_ncu_launch_list_step.json")
+    path = os.path.join(ROOT, "profiles", "r01c_ncu_launch_list_step.json")
     try:
         fams = json.load(open(path))["families"]
     except Exception:
@@ -192,7 +192,21 @@ def decode_bench(torch, nnm, device):
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
             assert len(toks) == 512 + 64
-            out[f"{tag}_b{B}"] = {"tokens_per_s": B * 64 / dt, "seconds": dt}
+            # the incremental step alone: (prefill + 64 tokens) - (prefill + 1 token), and what it streams from HBM:
+            # every weight once per step ((12 L C^2 + V C) elements) + the cached K/V of every sequence
+            t0 = time.perf_counter()
+            model.generate_tokens(prompt, 1024, 1, temperature=0.0)
+            torch.cuda.synchronize()
+            dt1 = time.perf_counter() - t0
+            step_s = max(dt - dt1, 1e-9) / 63
+            es = 2 if dtype == torch.bfloat16 else 4
+            w_bytes = (12 * CFG["L"] * CFG["C"] ** 2 + V * CFG["C"]) * es
+            kv_bytes = B * (512 + 32) * 2 * CFG["L"] * CFG["C"] * es          # mean context over the 64 steps
+            peak = measured_peaks()[0]["hbm_gbs"]
+            out[f"{tag}_b{B}"] = {"tokens_per_s": B * 64 / dt, "seconds": dt, "step_ms": step_s * 1e3,
+                                  "step_tokens_per_s": B / step_s,
+                                  "hbm_gbps": (w_bytes + kv_bytes) / step_s / 1e9,
+                                  "hbm_frac": (w_bytes + kv_bytes) / step_s / 1e9 / peak}
         del model
         torch.cuda.empty_cache()
     out["workload"] = "GPT-2 124M greedy generate_tokens: 512-token prompt + 64 new tokens (prefill included), context 1024"
@@ -359,7 +373,7 @@ def run_ours(args):
         peak = peaks["bf16_tflops_sustained"]
         roofline = {"kernel": name, "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                     "frac": achieved / peak, "traffic": ncu_traffic_per_launch(name),
-                    "traffic_source": "profiles/r01_ncu_launch_list_step.json (dram__bytes_read+write per launch, family mean)",
+                    "traffic_source": "profiles/r01c_ncu_launch_list_step.json (dram__bytes_read+write per launch, family mean)",
                     "peak_source": f"{which} (sustained: kernel timed inside a long step)",
                     "share_of_step": d["ms"] / step_ms, "launches_per_step": d["launches"],
                     "families_ms": {k: round(v["ms"], 3) for k, v in fam.items()}, "instrumented_step_ms": step_ms}

@@ -508,6 +508,12 @@ static bool use_pdl() {
     return on;
 }
 
+// CTAs per SM a GEMV grid may reach before a CTA takes more than one pass of columns (PENROZ_GEMV_GRID_CAP)
+static int gemv_grid_cap() {
+    static const int v = getenv("PENROZ_GEMV_GRID_CAP") ? atoi(getenv("PENROZ_GEMV_GRID_CAP")) : 24;
+    return v < 1 ? 1 : v;
+}
+
 template <typename T, int MB>
 static int launch_gemv_mb(const GemvParams& p, int pro, cudaStream_t st) {
     constexpr int R = GemvRows<T>::R;
@@ -515,7 +521,7 @@ static int launch_gemv_mb(const GemvParams& p, int pro, cudaStream_t st) {
     // (one finishing thread per output)
     int rpb = R;
     const int cap = 128 / MB;
-    while (rpb * 2 <= cap && (p.N + rpb - 1) / rpb > 6 * num_sms()) rpb *= 2;
+    while (rpb * 2 <= cap && (p.N + rpb - 1) / rpb > gemv_grid_cap() * num_sms()) rpb *= 2;
     const size_t smem = ((size_t)MB * p.K + (size_t)4 * rpb * MB + (pro == PRO_COMBINE ? (size_t)2 * MB * p.H * p.splits : 0)) * sizeof(float);
     PENROZ_REQUIRE(smem <= 200 * 1024, "gemv: K=%d needs %zu bytes of shared memory", p.K, smem);
     dim3 grid((p.N + rpb - 1) / rpb, (p.M + MB - 1) / MB);
@@ -549,7 +555,7 @@ static int gemv_grid_x(int N) {
     constexpr int R = GemvRows<T>::R;
     int rpb = R;
     const int cap = 128 / MB;
-    while (rpb * 2 <= cap && (N + rpb - 1) / rpb > 6 * num_sms()) rpb *= 2;
+    while (rpb * 2 <= cap && (N + rpb - 1) / rpb > gemv_grid_cap() * num_sms()) rpb *= 2;
     return (N + rpb - 1) / rpb;
 }
 template <typename T>
