@@ -175,7 +175,11 @@ int penroz_argmax_rows(const void* x, long long ld, int rows, int V, long long* 
  * Replaces one iteration of the generation loop (neural_net_model.py:465-469, incremental branch :382-386): embedding
  * at position `pos`, every block (LN, QKV, paged K/V append at `pos`, split-KV attention over pos+1 keys, proj+residual,
  * LN, fc+GELU, proj2+residual), final LN, LM head into logits_out [B,V] (model dtype) and, when argmax_out is not NULL,
- * the greedy token ids. `layers` is a HOST array; every pointer inside it is a device pointer. */
+ * the greedy token ids. `layers` is a HOST array; every pointer inside it is a device pointer.
+ * For B <= 16 the step runs as five launches per block (decode_fused.cu): LayerNorm, bias, GELU, residual and the K/V
+ * page write ride in the prologue / epilogue of weight-streaming GEMV kernels, the split-KV attention merges its
+ * partials inside a thread-block cluster, and consecutive launches overlap through programmatic dependent launch;
+ * larger batches take one kernel per op with tensor-core GEMMs. Same results up to summation order. */
 typedef struct penroz_gpt2_layer_t {
     const void *ln1_w, *ln1_b, *qkv_w, *qkv_b, *proj_w, *proj_b, *ln2_w, *ln2_b, *fc_w, *fc_b, *proj2_w, *proj2_b;
     void* kv_pool;
