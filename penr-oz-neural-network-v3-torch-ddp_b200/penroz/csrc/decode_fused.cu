@@ -605,6 +605,7 @@ static int decode_step_small_t(const long long* tokens, const void* wte, const v
                                void* qkv, void* att, void* g, float* part, float* amax_val, int* amax_idx, void* logits_out,
                                long long* argmax_out, int* err_flag, cudaStream_t st) {
     const int D = C / H;
+    PENROZ_REQUIRE(pos / KVP < max_pages, "gpt2_decode_step: position %d exceeds the block table (%d pages)", pos, max_pages);
     int rc = penroz_embed_fwd(tokens, wte, wpe, xa, B, 1, C, V, pos, dtype, dtype, err_flag, st);
     if (rc) return rc;
     const int t_len = pos + 1;
