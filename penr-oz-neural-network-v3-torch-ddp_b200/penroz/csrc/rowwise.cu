@@ -130,6 +130,53 @@ __global__ void layernorm_fwd_kernel(const TX* __restrict__ x, const TW* __restr
     }
 }
 
+// Same arithmetic with the row held in registers (J = ceil(C / 128) float4 per lane): one pass over global memory and
+// every load of the row in flight at once, instead of three dependent passes.
+template <typename TX, typename TW, typename TO, int J>
+__global__ void __launch_bounds__(256)
+layernorm_fwd_reg_kernel(const TX* __restrict__ x, const TW* __restrict__ gamma, const TW* __restrict__ beta,
+                         TO* __restrict__ out, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
+                         int C, float eps) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const TX* xr = x + (size_t)row * C;
+    float4 v[J];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int i = (lane + 32 * j) * 4;
+        v[j] = (i < C) ? load4(xr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+    }
+    const float mean = warp_sum(s) / (float)C;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int i = (lane + 32 * j) * 4;
+        if (i < C) {
+            const float a = v[j].x - mean, b = v[j].y - mean, c = v[j].z - mean, d = v[j].w - mean;
+            q += (a * a + b * b) + (c * c + d * d);
+        }
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)C + eps);
+    if (lane == 0) {
+        if (mean_out) mean_out[row] = mean;
+        if (rstd_out) rstd_out[row] = rstd;
+    }
+    TO* o = out + (size_t)row * C;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int i = (lane + 32 * j) * 4;
+        if (i < C) {
+            const float4 g = load4(gamma + i);
+            const float4 b = beta ? load4(beta + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            store4(o + i, make_float4((v[j].x - mean) * rstd * g.x + b.x, (v[j].y - mean) * rstd * g.y + b.y,
+                                      (v[j].z - mean) * rstd * g.z + b.z, (v[j].w - mean) * rstd * g.w + b.w));
+        }
+    }
+}
+
 // ------------------------------------------------------------------ LayerNorm backward
 // dx_total = add + rstd * (dy*g - mean(dy*g) - xhat * mean(dy*g*xhat)); written as TX and (optionally) a bf16 copy.
 // Column reductions (dgamma = sum dy*xhat, dbeta = sum dy, dcol = sum bf16-or-f32(dx_total)) are accumulated in
@@ -232,7 +279,7 @@ layernorm_bwd_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, const 
 // (few registers -> high occupancy -> HBM-bound), (2) a column kernel that re-reads dy, x and the written gradient
 // and accumulates dgamma/dbeta/dcol for 4 columns per thread over a slice of the rows.
 template <typename TX, typename TW, typename TG, int J>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (J <= 6) ? 3 : 1)
 layernorm_bwd_rows_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, const TW* __restrict__ gamma,
                           const float* __restrict__ mean, const float* __restrict__ rstd, const TX* __restrict__ add,
                           TX* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16, int rows, int C) {
@@ -242,8 +289,14 @@ layernorm_bwd_rows_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, c
     const TG* dyr = dy + (size_t)row * C;
     const TX* xr = x + (size_t)row * C;
     const float mu = mean[row], rs = rstd[row];
-    float4 dyg[J], xh[J];
+    float4 dyg[J], xh[J], ad[J];
     float s1 = 0.f, s2 = 0.f;
+    // the residual gradient does not depend on the row statistics: fetch it with dy and x, not after the reductions
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int i = (lane + 32 * j) * 4;
+        ad[j] = (add && i < C) ? load4(add + (size_t)row * C + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
     for (int j = 0; j < J; ++j) {
         const int i = (lane + 32 * j) * 4;
@@ -266,10 +319,7 @@ layernorm_bwd_rows_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, c
             r.y = rs * (dyg[j].y - s1 - xh[j].y * s2);
             r.z = rs * (dyg[j].z - s1 - xh[j].z * s2);
             r.w = rs * (dyg[j].w - s1 - xh[j].w * s2);
-            if (add) {
-                const float4 a = load4(add + (size_t)row * C + i);
-                r.x += a.x; r.y += a.y; r.z += a.z; r.w += a.w;
-            }
+            r.x += ad[j].x; r.y += ad[j].y; r.z += ad[j].z; r.w += ad[j].w;
             store4(dx + (size_t)row * C + i, r);
             if (dx_bf16) store4(dx_bf16 + (size_t)row * C + i, r);
         }
@@ -503,12 +553,21 @@ extern "C" int penroz_layernorm_fwd(const void* x, const void* gamma, const void
     PENROZ_REQUIRE(rows > 0 && C > 0, "layernorm_fwd: bad shape rows=%d C=%d", rows, C);
     cudaStream_t st = (cudaStream_t)stream;
     const int grid = (rows + 7) / 8;
-#define LN_FWD(TX, TW, TO) layernorm_fwd_kernel<TX, TW, TO><<<grid, 256, 0, st>>>((const TX*)x, (const TW*)gamma, (const TW*)beta, (TO*)out, mean, rstd, rows, C, eps)
+    const int J = (C + 127) / 128;
+    const bool reg = (C % 4 == 0) && J <= 16;
+#define LN_FWD_J(TX, TW, TO, j) layernorm_fwd_reg_kernel<TX, TW, TO, j><<<grid, 256, 0, st>>>((const TX*)x, (const TW*)gamma, (const TW*)beta, (TO*)out, mean, rstd, rows, C, eps)
+#define LN_FWD(TX, TW, TO)                                                                                    \
+    if (!reg) layernorm_fwd_kernel<TX, TW, TO><<<grid, 256, 0, st>>>((const TX*)x, (const TW*)gamma, (const TW*)beta, (TO*)out, mean, rstd, rows, C, eps); \
+    else if (J <= 1) LN_FWD_J(TX, TW, TO, 1); else if (J <= 2) LN_FWD_J(TX, TW, TO, 2);                        \
+    else if (J <= 4) LN_FWD_J(TX, TW, TO, 4); else if (J <= 6) LN_FWD_J(TX, TW, TO, 6);                        \
+    else if (J <= 8) LN_FWD_J(TX, TW, TO, 8); else if (J <= 13) LN_FWD_J(TX, TW, TO, 13);                      \
+    else LN_FWD_J(TX, TW, TO, 16)
     if (x_dtype == F32 && w_dtype == F32 && out_dtype == BF16) LN_FWD(float, float, __nv_bfloat16);
     else if (x_dtype == F32 && w_dtype == F32 && out_dtype == F32) LN_FWD(float, float, float);
     else if (x_dtype == BF16 && w_dtype == BF16 && out_dtype == BF16) LN_FWD(__nv_bfloat16, __nv_bfloat16, __nv_bfloat16);
     else { set_error("layernorm_fwd: unsupported dtypes x=%d w=%d out=%d", x_dtype, w_dtype, out_dtype); return PENROZ_ERR_ARG; }
 #undef LN_FWD
+#undef LN_FWD_J
     count_launch();
     return check_launch("layernorm_fwd");
 }
