@@ -155,6 +155,18 @@ size_t penroz_grad_norm_scratch_bytes(long long n);
 int penroz_grad_norm(const float* g, long long n, float max_norm, float* norm_out, float* mult_out, void* scratch,
                      size_t scratch_bytes, void* stream);
 
+/* ---- rank-0 training diagnostics ----
+ * Replaces, for CUDA tensors, the per-layer / per-weight summaries of _record_training_overall_progress
+ * (neural_net_model.py:743-777): t.mean(), t.std() (unbiased), a saturation fraction |t| > abs_threshold and
+ * torch.histogram(t.cpu(), density=True) -- which copies every activation to the host and bins it on one CPU thread.
+ * out (device, 7 + bins doubles) = {mean, std, min, max, saturated fraction, range lo, range hi, counts[bins]}.
+ * Counts follow ATen's CPU histogram for uniform bins step by step (float position estimate, local search against the
+ * torch.linspace edges, closed right edge, a constant tensor widens its range by 0.5 each side). One tensor = two
+ * passes over HBM; the caller reads `out` back with a single copy. */
+size_t penroz_tensor_stats_scratch_bytes(int bins);
+int penroz_tensor_stats(const void* x, long long n, int dtype, int bins, float abs_threshold, double* out,
+                        void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- KV-cache decode step ----
  * Replaces KVCache.append's torch.cat (kv_cache.py:41-68), the cache branch of CausalSelfAttention.forward
  * (neural_net_layers.py:83-92) and logits[:, -1, :].argmax (neural_net_model.py:393-394).

@@ -640,29 +640,51 @@ class NeuralNetworkModel(nn.Module):
                 hit = a.abs() > 5.0
             return hit.float().mean().item()
 
+        # |a| > threshold is the saturation test of every kind except these three (their own reductions below)
+        abs_threshold = {"batchnorm1d": 3.0, "tanh": 0.97, "sigmoid": 0.97}
+
+        def summary(t: Tensor, kind: str | None = None):
+            """(mean, std, saturated | None, histogram x, histogram y). CUDA tensors: one pass pair on the GPU and one
+            small host read (penroz_tensor_stats); host tensors: the reference's torch calls."""
+            if t.is_cuda and t.dtype in (torch.float32, torch.bfloat16) and t.numel() > 0:
+                from penroz import ops
+                own = kind is not None and kind not in ("embedding", "relu", "softmax")
+                mean, std, _, _, sat, lo, hi, counts = ops.tensor_stats(t, 100, abs_threshold.get(kind, 5.0) if own else 5.0)
+                edges = torch.linspace(lo, hi, 101, dtype=torch.float32)
+                width = (edges[1:] - edges[:-1]).double()
+                dens = (torch.tensor(counts, dtype=torch.float64) / (float(t.numel()) * width)).float()
+                if kind is not None and not own:
+                    sat = saturation(kind, t.float())
+                return mean, std, sat, edges[:-1].tolist(), dens.tolist()
+            x, y = self._density_histogram(t)
+            tf = t.float()
+            return tf.mean().item(), tf.std().item(), (saturation(kind, tf) if kind is not None else None), x, y
+
         layer_stats = []
         for layer, (a, g) in zip(self.layers, pairs):
             kind = layer.__class__.__name__.lower()
-            ax, ay = self._density_histogram(a)
+            mean, std, sat, ax, ay = summary(a, kind)
             entry = {"algo": kind,
-                     "activation": {"mean": a.float().mean().item(), "std": a.float().std().item(),
-                                    "saturated": saturation(kind, a.float()), "histogram": {"x": ax, "y": ay}},
+                     "activation": {"mean": mean, "std": std, "saturated": sat, "histogram": {"x": ax, "y": ay}},
                      "gradient": None}
             if g is not None:
-                gx, gy = self._density_histogram(g)
-                entry["gradient"] = {"mean": g.float().mean().item(), "std": g.float().std().item(),
-                                     "histogram": {"x": gx, "y": gy}}
+                mean, std, _, gx, gy = summary(g)
+                entry["gradient"] = {"mean": mean, "std": std, "histogram": {"x": gx, "y": gy}}
             layer_stats.append(entry)
         weight_stats = []
         for w in self._weights:
             if w is None:
                 weight_stats.append(None)
                 continue
-            gx, gy = self._density_histogram(w.grad)
+            gmean, gstd, _, gx, gy = summary(w.grad)
+            if w.is_cuda and w.dtype in (torch.float32, torch.bfloat16):
+                from penroz import ops
+                wmean, wstd = ops.tensor_stats(w.data, 1, 5.0)[:2]
+            else:
+                wmean, wstd = w.mean().item(), w.std().item()
             weight_stats.append({"shape": str(tuple(w.shape)),
-                                 "data": {"mean": w.mean().item(), "std": w.std().item()},
-                                 "gradient": {"mean": w.grad.mean().item(), "std": w.grad.std().item(),
-                                              "histogram": {"x": gx, "y": gy}}})
+                                 "data": {"mean": wmean, "std": wstd},
+                                 "gradient": {"mean": gmean, "std": gstd, "histogram": {"x": gx, "y": gy}}})
         self.stats = {"layers": layer_stats, "weights": weight_stats}
         log.info(f"Model {self.model_id} - Cost: {mean_cost:.4f} Overall Cost: {self.avg_cost:.4f}")
 

@@ -222,6 +222,20 @@ def grad_norm(g, max_norm, norm_out, mult_out, scratch=None):
                     stream())
 
 
+def tensor_stats(t, bins: int = 100, abs_threshold: float = 5.0):
+    """mean / std / min / max / saturated fraction and histogram counts of a CUDA tensor with one host read.
+    Returns (mean, std, min, max, saturated, lo, hi, counts[list of float])."""
+    t = t.detach()
+    if not t.is_contiguous():
+        t = t.contiguous()
+    out = torch.empty(7 + bins, device=t.device, dtype=torch.float64)
+    scratch = torch.empty(lib().tensor_stats_scratch_bytes(bins), device=t.device, dtype=torch.uint8)
+    lib().tensor_stats(ptr(t), t.numel(), dt(t), int(bins), float(abs_threshold), ptr(out), ptr(scratch),
+                       scratch.numel(), stream())
+    vals = out.tolist()
+    return vals[0], vals[1], vals[2], vals[3], vals[4], vals[5], vals[6], vals[7:]
+
+
 def kv_append(qkv2d, pool, block_table, B, S, H, D, t0):
     lib().kv_append(ptr(qkv2d), ptr(pool), ptr(block_table), block_table.shape[1], B, S, H, D, t0, dt(qkv2d), stream())
 

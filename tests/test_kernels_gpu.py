@@ -353,3 +353,63 @@ def test_decode_kernels(dev, dtype):
     am = ops.argmax_rows(lg, V=50257)
     assert torch.equal(am, lg[:, :50257].float().argmax(dim=-1))
     assert am[2].item() == 100
+
+
+# ------------------------------------------------------------------ rank-0 diagnostics
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_tensor_stats_match_torch_histogram(dev, dtype):
+    from penroz import ops
+    torch.manual_seed(11)
+    cases = [torch.randn(1000003, device=dev) * 3.0 + 0.5, torch.randn(257, 129, device=dev) ** 3,
+             torch.full((4097,), 1.25, device=dev), torch.rand(65536, device=dev) * 1e-3 - 5e-4,
+             torch.tensor([-2.0, 7.0], device=dev)]
+    for c in cases:
+        t = c.to(dtype)
+        mean, std, mn, mx, sat, lo, hi, counts = ops.tensor_stats(t, 100, 5.0)
+        ref = t.float().cpu()
+        h = torch.histogram(ref, bins=100)
+        assert counts == h.hist.tolist(), (dtype, tuple(c.shape))           # bin by bin, exactly
+        assert lo == h.bin_edges[0].item() and hi == h.bin_edges[-1].item()
+        assert mn == ref.min().item() and mx == ref.max().item()
+        assert abs(mean - ref.double().mean().item()) <= 1e-6 * max(1.0, abs(mean))
+        assert abs(std - ref.double().std().item()) <= 1e-6 * max(1.0, std)
+        assert abs(sat - (ref.abs() > 5.0).double().mean().item()) < 1e-12
+
+
+def test_training_stats_gpu_path_equals_host_path(dev):
+    """_record_training_overall_progress on CUDA tensors (penroz_tensor_stats) against the same method on host copies
+    (the reference's torch calls, neural_net_model.py:743-777)."""
+    from helpers import build_gpt, scratch_cwd
+    scratch_cwd()
+    m = build_gpt("stats", 2, 4, 128, 64, 65)
+    torch.manual_seed(5)
+    acts = [(torch.randn(4, 64, 128) * (1 + i), torch.randn(4, 64, 128) * 1e-3) for i in range(5)]
+    acts.append((torch.randn(4, 64, 65) * 4, torch.randn(4, 64, 65) * 1e-4))
+    for p in m.parameters():
+        p.grad = torch.randn_like(p) * 1e-2
+    m.progress = [{"cost": 4.0}, {"cost": 3.5}]
+    m._record_training_overall_progress(acts)
+    host = m.stats
+    m.to("cuda")
+    for p in m.parameters():
+        assert p.grad is not None and p.grad.is_cuda
+    m._record_training_overall_progress([(a.cuda(), g.cuda()) for a, g in acts])
+    gpu = m.stats
+
+    def close(a, b, path):
+        if isinstance(a, dict):
+            assert a.keys() == b.keys(), path
+            for k in a:
+                if k == "mean" and "std" in a:      # a mean near zero: fp32 (host) vs fp64 (GPU) summation, scale = std
+                    assert abs(a[k] - b[k]) <= 1e-5 * max(a["std"], 1e-30), (path, a[k], b[k])
+                else:
+                    close(a[k], b[k], path + "/" + k)
+        elif isinstance(a, list):
+            assert len(a) == len(b), path
+            for i, (x, y) in enumerate(zip(a, b)):
+                close(x, y, f"{path}[{i}]")
+        elif isinstance(a, float):
+            assert abs(a - b) <= 2e-5 * max(abs(a), abs(b), 1e-30) + 1e-12, (path, a, b)
+        else:
+            assert a == b, (path, a, b)
+    close(host, gpu, "stats")
