@@ -24,7 +24,9 @@ import platform
 import random
 import shutil
 import tempfile
+import threading
 import time
+from collections import OrderedDict
 from contextlib import nullcontext
 from datetime import datetime as dt
 from typing import Optional, Tuple
@@ -56,6 +58,49 @@ from penroz.plan import match_gpt2
 
 log = logging.getLogger(__name__)
 MODELS_FOLDER = "models"
+
+# ---------------------------------------------------------------------------------------------------- residency
+# The service deserializes the model on EVERY /generate/, /output/, /evaluate/, /progress/ and /stats/ request
+# (main.py:405,415,424,478,489): torch.load of weights + AdamW moments (2.6 GB for 124M) and, for inference, a move to
+# the GPU -- seconds, against tens of milliseconds for the generation itself. SURVEY 8f row n2: keep the last few
+# models resident in the process. An entry is valid while the cached file is byte-for-byte the one it was loaded from
+# (same mtime_ns and size), so a training process rewriting the file invalidates it; the on-disk format is unchanged.
+# Those requests only read the model, but generation attaches its KV cache to the layers, so calls that run the model
+# take the entry's lock. PENROZ_MODEL_CACHE=0|1 (default: on when a GPU is visible), PENROZ_MODEL_CACHE_SIZE (2).
+_RESIDENT: "OrderedDict[str, tuple]" = OrderedDict()      # cached-file path -> (mtime_ns, size, model, RLock)
+_RESIDENT_GUARD = threading.Lock()
+
+
+def _residency_on() -> bool:
+    flag = os.environ.get("PENROZ_MODEL_CACHE")
+    if flag is not None:
+        return flag not in ("0", "false", "False", "")
+    return torch.cuda.is_available()
+
+
+def _file_stamp(path: str):
+    st = os.stat(path)
+    return st.st_mtime_ns, st.st_size
+
+
+class _Exclusive:
+    """Context manager: the resident entry's lock when `model` is shared through the residency cache, else nothing."""
+
+    def __init__(self, model):
+        key = model.__dict__.get("_resident_key")
+        with _RESIDENT_GUARD:
+            entry = _RESIDENT.get(key) if key else None
+        self.lock = entry[3] if entry is not None and entry[2] is model else None
+
+    def __enter__(self):
+        if self.lock is not None:
+            self.lock.acquire()
+        return self
+
+    def __exit__(self, *exc):
+        if self.lock is not None:
+            self.lock.release()
+        return False
 
 
 def _now_status(code: str, message: str) -> dict:
@@ -157,6 +202,13 @@ class NeuralNetworkModel(nn.Module):
         if chatty:
             log.info(f"Caching model to {shm_path}...")
         torch.save(payload, shm_path, pickle_protocol=5)
+        with _RESIDENT_GUARD:
+            entry = _RESIDENT.get(shm_path)
+            if entry is not None:
+                if entry[2] is self:        # the file now holds exactly this object's state: keep it resident
+                    _RESIDENT[shm_path] = _file_stamp(shm_path) + (self, entry[3])
+                else:
+                    del _RESIDENT[shm_path]
         if chatty:
             log.info(f"Model cached successfully: {shm_path}")
             log.info(f"Offload flushing model cache {shm_path} to {disk_path}...")
@@ -175,6 +227,16 @@ class NeuralNetworkModel(nn.Module):
                     shutil.copyfile(disk_path, shm_path)
                 if ddp.is_ddp() and dist.is_available() and dist.is_initialized():
                     dist.barrier()
+            resident = _residency_on()
+            if resident:
+                stamp = _file_stamp(shm_path)
+                with _RESIDENT_GUARD:
+                    entry = _RESIDENT.get(shm_path)
+                    if entry is not None and entry[:2] == stamp:
+                        _RESIDENT.move_to_end(shm_path)
+                        if chatty:
+                            log.info(f"Model {model_id} is resident (unchanged {shm_path})")
+                        return entry[2]
             if chatty:
                 log.info(f"Retrieving model from {shm_path}...")
             data = torch.load(shm_path, weights_only=False)
@@ -198,6 +260,14 @@ class NeuralNetworkModel(nn.Module):
         model.status = data["status"]
         if chatty:
             log.info(f"Model {model_id} is fully loaded")
+        if resident and _file_stamp(shm_path) == stamp:       # not rewritten while it was being read
+            model.__dict__["_resident_key"] = shm_path
+            with _RESIDENT_GUARD:
+                _RESIDENT[shm_path] = stamp + (model, threading.RLock())
+                _RESIDENT.move_to_end(shm_path)
+                keep = max(1, int(os.environ.get("PENROZ_MODEL_CACHE_SIZE", "2")))
+                while len(_RESIDENT) > keep:
+                    _RESIDENT.popitem(last=False)
         return model
 
     @classmethod
@@ -234,6 +304,8 @@ class NeuralNetworkModel(nn.Module):
     @classmethod
     def delete(cls, model_id: str):
         disk_path = cls.get_model_path(model_id)
+        with _RESIDENT_GUARD:
+            _RESIDENT.pop(os.path.join(cls.SHM_PATH, disk_path), None)
         try:
             os.remove(os.path.join(cls.SHM_PATH, disk_path))
             if os.path.exists(disk_path):
@@ -281,6 +353,10 @@ class NeuralNetworkModel(nn.Module):
     @torch.no_grad()
     def compute_output(self, input_data: list, target: list | int | None = None) -> Tuple[list, float]:
         """Activated output of the last layer and, with a target, the cost — no training (/output/)."""
+        with _Exclusive(self):
+            return self._compute_output(input_data, target)
+
+    def _compute_output(self, input_data, target):
         if self.training or any(m.training for m in self.modules()):    # eval() walks ~170 modules: skip when already there
             self.eval()
         self.layers.training = False
@@ -301,6 +377,10 @@ class NeuralNetworkModel(nn.Module):
     def evaluate_model(self, dataset_id: str, target_dataset_id: str | None, shard: int,
                        epochs: int, batch_size: int, block_size: int, step_size: int) -> float:
         """Average cost over `epochs` loader windows (each re-used for every step), no training (/evaluate/)."""
+        with _Exclusive(self):
+            return self._evaluate_model(dataset_id, target_dataset_id, shard, epochs, batch_size, block_size, step_size)
+
+    def _evaluate_model(self, dataset_id, target_dataset_id, shard, epochs, batch_size, block_size, step_size):
         if self.training or any(m.training for m in self.modules()):    # eval() walks ~170 modules: skip when already there
             self.eval()
         self.layers.training = False
@@ -440,7 +520,14 @@ class NeuralNetworkModel(nn.Module):
         return torch.multinomial(probs.float(), num_samples=1)
 
     def _token_stream(self, input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink):
-        """Shared decode loop: yields each new token id (row 0) and leaves the full context in sink[0]."""
+        """Shared decode loop: yields each new token id (row 0) and leaves the full context in sink[0]. A model shared
+        through the residency cache is held exclusively until the stream ends (generation attaches its KV cache to
+        the layers)."""
+        with _Exclusive(self):
+            yield from self._token_stream_locked(input_context, block_size, max_new_tokens, temperature, top_k,
+                                                 stop_token, sink)
+
+    def _token_stream_locked(self, input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink):
         context, softmax_layer = self._prepare_generation(input_context, max_new_tokens, temperature, top_k)
         cache, positions = self._attach_kv_cache()
         try:

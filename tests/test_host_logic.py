@@ -231,3 +231,47 @@ def test_reference_test_suite_passes_against_the_dropin_modules(tmp_path):
     tail = res.stdout[-1500:]
     assert res.returncode == 0, tail
     assert "151 passed" in tail, tail
+
+
+def test_model_residency_cache(monkeypatch):
+    """deserialize() keeps the last models resident while their cached file is unchanged
+    (the service deserializes on every request, main.py:405-489); a rewritten file, delete() and the size limit evict."""
+    import time
+    import neural_net_model as nnm
+    scratch_cwd()
+    monkeypatch.setenv("PENROZ_MODEL_CACHE", "1")
+    nnm._RESIDENT.clear()
+    a = build_gpt("res_a", 1, 2, 32, 16, 11)
+    a.serialize()
+    m1 = nnm.NeuralNetworkModel.deserialize("res_a")
+    m2 = nnm.NeuralNetworkModel.deserialize("res_a")
+    assert m1 is m2 and m1 is not a                      # second request: no torch.load, the same resident object
+    for k, v in a.state_dict().items():
+        assert torch.equal(v, m1.state_dict()[k])
+    # the resident object runs under its entry's lock; an unrelated object takes none
+    assert nnm._Exclusive(m1).lock is not None and nnm._Exclusive(a).lock is None
+    assert m1.generate_tokens([[1, 2, 3]], 16, 4, temperature=0.0) == m2.generate_tokens([[1, 2, 3]], 16, 4, temperature=0.0)
+    # another writer (a training process) rewrites the file: the entry is stale, the next request reloads
+    time.sleep(0.01)
+    with torch.no_grad():
+        a.layers[0][0].weight.add_(1.0)
+    a.serialize()
+    m3 = nnm.NeuralNetworkModel.deserialize("res_a")
+    assert m3 is not m1 and torch.equal(m3.state_dict()["layers.0.0.weight"], a.state_dict()["layers.0.0.weight"])
+    # the resident object serialising itself stays resident
+    m3.progress.append({"cost": 1.0})
+    m3.serialize()
+    assert nnm.NeuralNetworkModel.deserialize("res_a") is m3
+    # size limit (2) and delete()
+    for name in ("res_b", "res_c"):
+        build_gpt(name, 1, 2, 32, 16, 11).serialize()
+        nnm.NeuralNetworkModel.deserialize(name)
+    assert len(nnm._RESIDENT) == 2 and not any("res_a" in k for k in nnm._RESIDENT)
+    nnm.NeuralNetworkModel.delete("res_c")
+    assert len(nnm._RESIDENT) == 1
+    with pytest.raises(KeyError):
+        nnm.NeuralNetworkModel.deserialize("res_c")
+    # switched off: every call loads afresh, as the reference does
+    monkeypatch.setenv("PENROZ_MODEL_CACHE", "0")
+    assert nnm.NeuralNetworkModel.deserialize("res_b") is not nnm.NeuralNetworkModel.deserialize("res_b")
+    nnm._RESIDENT.clear()
