@@ -318,7 +318,11 @@ class NeuralNetworkModel(nn.Module):
         """Returns (output of every top-level layer, cost). cost is an empty tensor without a target; cross entropy
         on the logits when the model ends in a Softmax layer, else MSE (reference: neural_net_model.py:250-271)."""
         engine = self._engine()
-        if engine is not None and input_tensor.is_cuda and not input_tensor.is_floating_point():
+        # A KV cache attached to the attention layers (the int8 TurboQuantKVCache, or a caller's own cache object) lives
+        # in the layers' forward: only the module composition honours it. The fused decode step never comes through
+        # here -- _generate_next_token drives the engine directly with its paged cache.
+        cache_attached = any(layer._kv_cache is not None for layer in self._find_attention_layers())
+        if engine is not None and input_tensor.is_cuda and not input_tensor.is_floating_point() and not cache_attached:
             return self._forward_fused(engine, input_tensor, target, skip_softmax)
         run = self.layers[:-1] if (skip_softmax and self._is_softmax_last) else self.layers
         outputs = []

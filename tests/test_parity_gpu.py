@@ -242,3 +242,22 @@ def test_fused_small_batch_decode_step_matches_unfused(env, monkeypatch, dtype, 
                 kf = sf.pools[layer][page, :, :, :used].float()
                 kp = sp.pools[layer][page, :, :, :used].float()
                 assert (kf - kp).abs().max().item() <= tol * max(1.0, kp.abs().max().item())
+
+
+def test_int8_kv_cache_generation_on_cuda_follows_the_layers(env, monkeypatch):
+    """TURBO_QUANT_KV_CACHE=1 (kv_cache.py:101-195): the int8 cache lives in the attention layers' forward, so on CUDA
+    generation must run the module composition with the cache attached -- same tokens as the same model on the CPU --
+    and must NOT silently decode without history through the fused forward."""
+    import kv_cache
+    monkeypatch.setattr(kv_cache, "TURBO_QUANT_ENABLED", True)
+    monkeypatch.setenv("PENROZ_INFERENCE_DEVICE", "cpu")
+    m = build_gpt("tq", 2, 4, 128, 64, 65)
+    prompt = [[1, 5, 9, 2, 7]]
+    cpu_tokens = m.generate_tokens(prompt, 64, 24, temperature=0.0)
+    monkeypatch.delenv("PENROZ_INFERENCE_DEVICE")
+    m.to("cuda")
+    gpu_tokens = m.generate_tokens(prompt, 64, 24, temperature=0.0)
+    assert gpu_tokens == cpu_tokens
+    monkeypatch.setattr(kv_cache, "TURBO_QUANT_ENABLED", False)
+    plain = m.generate_tokens(prompt, 64, 24, temperature=0.0)      # fused step, exact cache
+    assert len(plain) == len(gpu_tokens)
