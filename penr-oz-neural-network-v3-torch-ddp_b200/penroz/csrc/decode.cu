@@ -7,8 +7,14 @@
 // Here K/V live in a page pool [n_pages][2][H][PAGE][D]; a per-sequence block table maps position -> page, so an
 // append writes only the new token (O(1)) and attention streams each cached byte exactly once. All HBM-bound.
 #include "common.cuh"
+#include <stdlib.h>
+#include <string.h>
 
 namespace penroz {
+
+// decode_fused.cu: split-KV attention with the cluster merge; returns 1 when the shape is not covered
+int attn_decode_cluster(const void* qkv, const void* pool, const int* block_table, int max_pages, void* out, int B,
+                        int H, int D, int t_len, int dtype, cudaStream_t st);
 
 constexpr int KV_PAGE = 64;
 
@@ -248,6 +254,11 @@ extern "C" int penroz_attn_decode(const void* qkv, const void* pool, const int* 
     PENROZ_REQUIRE(B <= 65535 && H <= 65535, "attn_decode: B/H too large for the launch grid");
     PENROZ_REQUIRE(scratch && scratch_bytes >= penroz_attn_decode_scratch_bytes(B, H, D, t_len), "attn_decode: scratch too small");
     cudaStream_t st = (cudaStream_t)stream;
+    if (!getenv("PENROZ_DECODE_ATTN") || strcmp(getenv("PENROZ_DECODE_ATTN"), "split")) {
+        // one thread-block cluster per head, partials merged through distributed shared memory (decode_fused.cu)
+        const int rc = attn_decode_cluster(qkv, pool, block_table, max_pages, out, B, H, D, t_len, dtype, st);
+        if (rc <= 0) return rc;     // done or failed; 1 = shape not covered, use the two-kernel form below
+    }
     const int splits = decode_splits(B, H, t_len);
     const int chunk = (t_len + splits - 1) / splits;
     const size_t smem = (size_t)(D + chunk) * sizeof(float);

@@ -595,6 +595,45 @@ bool decode_small_supported(int B, int C, int H, int dtype) {
     return lpk >= 1 && lpk <= 32 && (lpk & (lpk - 1)) == 0;
 }
 
+// Split-KV attention for ANY batch with the cluster merge (what penroz_attn_decode runs when the head dimension fits
+// the lane layout): out [B, H*D]. Returns PENROZ_OK, or 1 when the shape is not covered (the caller falls back to the
+// two-kernel form).
+int attn_decode_cluster(const void* qkv, const void* pool, const int* block_table, int max_pages, void* out, int B,
+                        int H, int D, int t_len, int dtype, cudaStream_t st) {
+    const int vn = (dtype == F32) ? 4 : 8;
+    if (D % vn) return 1;
+    const int lpk = D / vn;
+    if (lpk < 1 || lpk > 32 || (lpk & (lpk - 1)) || D < 8) return 1;
+    // as many CTAs per head as keeps ~2 waves of 256-thread CTAs in flight (8 per SM), at least 32 keys each
+    int splits = 1;
+    const long long room = 16LL * num_sms();
+    while (splits * 2 <= 8 && splits * 2 * 32 <= t_len + 31 && (long long)B * H * splits * 2 <= room) splits *= 2;
+    const int chunk = (t_len + splits - 1) / splits;
+    const size_t smem = (size_t)(chunk + (kAttnWarps + 1) * D + 2 + chunk / KVP + 2) * sizeof(float);
+    if (smem > 48 * 1024) return 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(splits, H, B);
+    cfg.blockDim = dim3(kAttnWarps * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = splits; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    const float scale = 1.0f / sqrtf((float)D);
+    cudaError_t e;
+    if (dtype == F32)
+        e = cudaLaunchKernelEx(&cfg, attn_decode_split2_kernel<float, true>, (const float*)qkv, (const float*)pool,
+                               block_table, max_pages, (float*)nullptr, H, D, t_len, chunk, scale, (float*)out);
+    else
+        e = cudaLaunchKernelEx(&cfg, attn_decode_split2_kernel<__nv_bfloat16, true>, (const __nv_bfloat16*)qkv,
+                               (const __nv_bfloat16*)pool, block_table, max_pages, (float*)nullptr, H, D, t_len, chunk,
+                               scale, (__nv_bfloat16*)out);
+    if (e != cudaSuccess) { set_error("attn_decode cluster launch: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+    count_launch();
+    return check_launch("attn_decode_cluster");
+}
+
 size_t decode_small_extra_bytes(int B) { return (size_t)B * kAmaxSlots * 8 + 256; }
 
 template <typename T>
@@ -614,7 +653,8 @@ static int decode_step_small_t(const long long* tokens, const void* wte, const v
     int splits = fused_splits(B, H, t_len);
     if (use_cluster) {
         int s2 = 1;
-        while (s2 * 2 <= 8 && s2 * 2 * 32 <= t_len + 31) s2 *= 2;
+        const long long room = 16LL * num_sms();
+        while (s2 * 2 <= 8 && s2 * 2 * 32 <= t_len + 31 && (long long)B * H * s2 * 2 <= room) s2 *= 2;
         splits = s2;
     }
     const int chunk = (t_len + splits - 1) / splits;
