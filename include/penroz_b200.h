@@ -117,6 +117,12 @@ int penroz_colsum_static(const void* X, long long ld, int M, int N, float* out, 
 /* ---- dtype cast of a flat buffer (autocast's per-step weight cast, done once per optimizer step here) ---- */
 int penroz_cast(const void* in, void* out, long long n, int in_dtype, int out_dtype, void* stream);
 
+/* ---- y += alpha * x over flat fp32 buffers, alpha in device memory ----
+ * What autograd's AccumulateGrad does per parameter when `cost.backward()` is called on the cost forward() returned
+ * (neural_net_model.py:250-271, :650-653): here ONE pass over the flat gradient buffer, scaled by the incoming
+ * gradient of the cost without reading it on the host. */
+int penroz_axpy_f32(float* y, const float* x, const float* alpha, long long n, void* stream);
+
 /* ---- causal self-attention on the packed [B,T,3C] QKV buffer (exact fp32 arithmetic path) ----
  * Replaces CausalSelfAttention.forward, GPT-2 branch (neural_net_layers.py:59-95) and its backward.
  * out is [B,T,C]; lse is [B,H,T] fp32. D in {32, 64, 128}. */

@@ -341,18 +341,34 @@ class NeuralNetworkModel(nn.Module):
         return outputs, nn.functional.cross_entropy(logits, target)
 
     def _forward_fused(self, engine, input_tensor, target, skip_softmax):
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            raise NotImplementedError(
-                "forward() under autograd is not available on the fused CUDA path: train through train_model() "
-                "(hand-written backward), or call forward() inside torch.no_grad()/inference_mode()")
         if target is not None and not (target.ndim == input_tensor.ndim):
             raise ValueError("fused forward expects a target of the same shape as the token input")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            if target is None or ddp.ddp_world_size() > 1:
+                raise NotImplementedError(
+                    "forward() under autograd on the fused CUDA path needs a target (the cost is what backward() "
+                    "starts from) and a single process; train through train_model() for DDP, or call forward() "
+                    "inside torch.no_grad()/inference_mode()")
+            return self._forward_fused_autograd(engine, input_tensor, target, skip_softmax)
         logits, loss, acts = engine.forward_infer(input_tensor, target, pos_offset=self._plan.wpe.position_offset,
                                                    collect=True)
         if self._is_softmax_last and not skip_softmax:
             acts.append(self.layers[-1](logits))
         cost = loss if loss is not None else torch.empty(0)
         return acts, cost
+
+    def _forward_fused_autograd(self, engine, input_tensor, target, skip_softmax):
+        """`acts, cost = model(x, y); cost.backward(); optimizer.step()` on CUDA (the reference's own step,
+        neural_net_model.py:629-653,677, written by hand by a caller): forward + hand-written backward run now,
+        cost.backward() folds the pending gradients into .grad (engine.forward_with_pending_grads). Activations come
+        back detached; under torch.autocast(bfloat16) the bf16 path runs, else the exact fp32 one."""
+        use_amp = torch.is_autocast_enabled("cuda") if hasattr(torch, "is_autocast_enabled") else False
+        loss, kept = engine.forward_with_pending_grads(input_tensor, target, use_amp)
+        acts = [a for a, _ in _FusedStepper._stat_pairs(kept)]
+        if self._is_softmax_last and not skip_softmax:
+            acts.append(self.layers[-1](acts[-1]))
+        anchor = next(p for p in self.parameters() if p.requires_grad)
+        return acts, _PendingGradCost.apply(anchor, engine, loss)
 
     @torch.no_grad()
     def compute_output(self, input_data: list, target: list | int | None = None) -> Tuple[list, float]:
@@ -778,6 +794,21 @@ class NeuralNetworkModel(nn.Module):
                                  "gradient": {"mean": gmean, "std": gstd, "histogram": {"x": gx, "y": gy}}})
         self.stats = {"layers": layer_stats, "weights": weight_stats}
         log.info(f"Model {self.model_id} - Cost: {mean_cost:.4f} Overall Cost: {self.avg_cost:.4f}")
+
+
+class _PendingGradCost(torch.autograd.Function):
+    """The cost of a fused forward as an autograd node: its backward adds grad_output x (the gradients the engine
+    already computed) to the parameters' .grad buffer."""
+
+    @staticmethod
+    def forward(ctx, anchor, engine, loss):
+        ctx.engine = engine
+        return loss.detach().clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        ctx.engine.backward_pending(grad_out)
+        return None, None, None
 
 
 class _TorchStepper:

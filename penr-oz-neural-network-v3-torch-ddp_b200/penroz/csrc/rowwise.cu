@@ -486,6 +486,21 @@ __global__ void cast_kernel(const TI* __restrict__ in, TO* __restrict__ out, siz
         for (size_t k = n & ~(size_t)3; k < n; ++k) out[k] = from_f32<TO>(to_f32(in[k]));
 }
 
+// y += alpha * x over a flat fp32 buffer, alpha read from device memory (no host sync)
+__global__ void axpy_f32_kernel(float* __restrict__ y, const float* __restrict__ x, const float* __restrict__ alpha, size_t n) {
+    const float a = *alpha;
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+    for (; i + 3 < n; i += stride) {
+        float4 yv = *reinterpret_cast<const float4*>(y + i);
+        const float4 xv = *reinterpret_cast<const float4*>(x + i);
+        yv.x = fmaf(a, xv.x, yv.x); yv.y = fmaf(a, xv.y, yv.y); yv.z = fmaf(a, xv.z, yv.z); yv.w = fmaf(a, xv.w, yv.w);
+        *reinterpret_cast<float4*>(y + i) = yv;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        for (size_t k = n & ~(size_t)3; k < n; ++k) y[k] = fmaf(a, x[k], y[k]);
+}
+
 template <int J, bool DCOL, typename TX, typename TW, typename TG>
 static void launch_ln_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
                           const void* add, void* dx, void* dx_bf16, float* scratch, int rows, int C, int grid,
@@ -707,6 +722,15 @@ extern "C" int penroz_cast(const void* in, void* out, long long n, int in_dtype,
     else { set_error("cast: unsupported %d -> %d", in_dtype, out_dtype); return PENROZ_ERR_ARG; }
     count_launch();
     return check_launch("cast");
+}
+
+extern "C" int penroz_axpy_f32(float* y, const float* x, const float* alpha, long long n, void* stream) {
+    PENROZ_REQUIRE(y && x && alpha && n > 0, "axpy_f32: bad arguments");
+    PENROZ_REQUIRE((((uintptr_t)y | (uintptr_t)x) & 15) == 0, "axpy_f32: buffers must be 16-byte aligned");
+    const int grid = grid_for((size_t)(n + 3) / 4, 256);
+    axpy_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(y, x, alpha, (size_t)n);
+    count_launch();
+    return check_launch("axpy_f32");
 }
 
 // ------------------------------------------------------------------ column sums without caller scratch

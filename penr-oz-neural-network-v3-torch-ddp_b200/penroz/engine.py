@@ -483,6 +483,62 @@ class Gpt2Engine:
             gs.ready("embed")
         return loss
 
+    # ------------------------------------------------------------------ forward() under autograd
+    def forward_with_pending_grads(self, idx, targets, use_amp: bool):
+        """forward() called with gradients enabled (a caller's own training loop: cost.backward(); optimizer.step()).
+        The hand-written backward cannot be replayed later by autograd, so it runs now, into a PENDING gradient buffer
+        of the flat layout; backward_pending() then adds it, scaled by the cost's incoming gradient, to the real
+        .grad buffer. Returns (loss, kept activations / activation gradients)."""
+        were_none = [p.grad is None for p in self.parameters]
+        self.setup_training(use_amp)
+        fl = self.flat
+        self._own_step_tensors(True)
+        if getattr(fl, "g_pending", None) is None:
+            fl.g_pending = torch.zeros_like(fl.g)
+        else:
+            fl.g_pending.zero_()
+        real, fl.g = fl.g, fl.g_pending
+        try:
+            self.keep_for_stats = {}
+            loss = self.train_micro_step(idx, targets, 1.0, sync_grads=False, keep_stats=True)
+            kept = self.keep_for_stats
+        finally:
+            fl.g = real
+            self.keep_for_stats = None
+        for p, none in zip(self.parameters, were_none):     # zero_grad(set_to_none=True) stays visible until backward
+            if none:
+                p.grad = None
+        return loss, kept
+
+    def _own_step_tensors(self, separate: bool):
+        """The fused AdamW keeps ONE `step` tensor shared by every parameter's optimizer state (one fill per step).
+        A stock torch optimizer.step() increments each state's tensor, so before handing the parameters to a caller's
+        own loop every state gets its own tensor; the fused optimizer takes them back (max of the counts)."""
+        if self.optimizer is None or getattr(self, "_steps_separate", False) == separate:
+            return
+        states = [self.optimizer.state[p] for p in self.parameters if p in self.optimizer.state]
+        if separate:
+            for st in states:
+                st["step"] = torch.tensor(float(self.step_count), dtype=torch.float32)
+        else:
+            counts = [int(st["step"].item()) if torch.is_tensor(st["step"]) else int(st["step"]) for st in states]
+            self.step_count = max(counts + [self.step_count])
+            self.flat.step_tensor.fill_(float(self.step_count))
+            for st in states:
+                st["step"] = self.flat.step_tensor
+        self._steps_separate = separate
+
+    def backward_pending(self, grad_out):
+        fl = self.flat
+        dropped = [p for p in self.parameters if p.grad is None]
+        if len(dropped) == len(self.parameters):
+            fl.g.zero_()
+        else:
+            for p in dropped:
+                fl.grad(p).zero_()
+        fl.rebind_grads()
+        ops.axpy_(fl.g, fl.g_pending, grad_out.detach().to(torch.float32).reshape(()).contiguous())
+
     def _scratch(self, M, widest):
         C, H = self.plan.n_embd, self.plan.n_head
         need = max(ops.lib().layernorm_bwd_scratch_bytes(M, C), ops.lib().colsum_scratch_bytes(M, widest),
@@ -510,6 +566,7 @@ class Gpt2Engine:
             raise PenrozError("fused AdamW expects the reference's single parameter group (mappers.py:267-274)")
         if grp.get("amsgrad", False) or grp.get("maximize", False):
             raise PenrozError("fused AdamW does not implement amsgrad / maximize")
+        self._own_step_tensors(False)
         self.step_count += 1
         mult = None
         if self.clip_grad_norm > 0.0:

@@ -148,6 +148,12 @@ def cast(src, dst):
     return dst
 
 
+def axpy_(y, x, alpha):
+    """y += alpha * x (flat fp32 CUDA buffers; alpha a 0-dim fp32 CUDA tensor)."""
+    lib().axpy_f32(ptr(y), ptr(x), ptr(alpha), y.numel(), stream())
+    return y
+
+
 def attn_fwd(qkv, H, want_lse=True, out=None, lse=None):
     """qkv [B,T,3C] -> (out [B,T,C], lse [B,H,T])."""
     B, T, C3 = qkv.shape

@@ -261,3 +261,52 @@ def test_int8_kv_cache_generation_on_cuda_follows_the_layers(env, monkeypatch):
     monkeypatch.setattr(kv_cache, "TURBO_QUANT_ENABLED", False)
     plain = m.generate_tokens(prompt, 64, 24, temperature=0.0)      # fused step, exact cache
     assert len(plain) == len(gpu_tokens)
+
+
+def test_forward_under_autograd_on_cuda(env, golden):
+    """A caller's own training loop on the drop-in -- zero_grad(); acts, cost = model(x, y); cost.backward();
+    optimizer.step() -- against the reference's gradients and its first training losses (the same loop is what
+    train_model runs, neural_net_model.py:622-677)."""
+    from penroz import _lib
+    g, meta = golden
+    m = build_gpt("bridge", 2, 4, 128, 64, 65)
+    m.to("cuda")
+    px = torch.tensor(g["tiny/probe_x"], device=env)
+    py = torch.tensor(g["tiny/probe_y"], device=env)
+    m.optimizer.zero_grad()                                   # set_to_none=True: every .grad is None
+    n0 = _lib.lib().launch_count()
+    acts, cost = m(px, py, skip_softmax=True)
+    assert cost.requires_grad and len(acts) == 6 and _lib.lib().launch_count() - n0 > 40
+    assert all(p.grad is None for p in m.parameters())        # nothing lands before backward()
+    np.testing.assert_allclose(cost.item(), float(g["tiny/init_loss"]), rtol=1e-5)
+    np.testing.assert_allclose(acts[-1].float().cpu().numpy(), g["tiny/init_logits"], rtol=1e-4, atol=2e-6)
+    (cost * 0.5).backward()
+    for name, p in m.named_parameters():
+        ref = 0.5 * g["tiny/init_grad/" + name]
+        got = p.grad.cpu().numpy()
+        assert np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12) < 1e-4, name
+    # accumulate the other half: gradients add up like autograd's AccumulateGrad
+    acts, cost = m(px, py, skip_softmax=True)
+    (cost * 0.5).backward()
+    for name, p in m.named_parameters():
+        ref = g["tiny/init_grad/" + name]
+        assert np.abs(p.grad.cpu().numpy() - ref).max() / (np.abs(ref).max() + 1e-12) < 1e-4, name
+    # the reference's step, hand-written, on its own data windows: first training losses
+    from penroz import shards
+    m2 = build_gpt("bridge2", 2, 4, 128, 64, 65)
+    m2.to("cuda")
+    ld = shards.Loader("synth65", 0, 0, 16 * 64, 16 * 64)
+    losses = []
+    for _ in range(5):
+        x, y = (torch.tensor(a, dtype=torch.long).view(16, 64).to(env) for a in ld.next_batch())
+        m2.optimizer.zero_grad()
+        _, c = m2(x, y, skip_softmax=True)
+        c.backward()
+        m2.optimizer.step()                                   # stock torch AdamW on the flat-buffer views
+        losses.append(c.item())
+    np.testing.assert_allclose(losses, g["tiny/train_loss"][:5], rtol=1e-4)
+    # hand-over to the fused optimizer: it continues from the step count torch's AdamW reached
+    assert float(m2.optimizer.state_dict()["state"][0]["step"]) == 5.0
+    m2.train_model("synth65", 0, 2, 16, 64, 16)
+    assert float(m2.optimizer.state_dict()["state"][0]["step"]) == 7.0
+    assert float(m2.optimizer.state_dict()["state"][27]["step"]) == 7.0
