@@ -382,7 +382,9 @@ class Gpt2Engine:
         loss = torch.zeros((), device=self.device, dtype=torch.float32)
         ops.ce_count_valid(targets, n_valid)
         Vp = _round_up(V, 64)
-        rows_per = min(M, self.head_chunk_rows)
+        # equal chunks (a short tail chunk leaves the K = V data-gradient GEMM with a third of the SMs: 0.5 ms)
+        n_chunks = max(1, -(-M // self.head_chunk_rows))
+        rows_per = min(M, _round_up(-(-M // n_chunks), 128))
         if keep_stats:
             rows_per = M
         logits = buf("logits", (rows_per, Vp), act)
