@@ -23,10 +23,6 @@ constexpr int AT_BM = 128;   // query rows per tile
 constexpr int AT_BN = 128;   // keys per tile
 constexpr int AT_D = 64;
 
-__device__ __forceinline__ uint64_t at_desc(uint32_t saddr, uint32_t lbo_enc, uint32_t sbo_enc) {
-    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)lbo_enc << 16) | ((uint64_t)sbo_enc << 32) |
-           (1ull << 46) | (2ull << 61);
-}
 // idesc: fp32 accum, bf16 x bf16, majors, N, M=128
 __device__ __forceinline__ uint32_t at_idesc(int a_mn, int b_mn, int N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |

@@ -17,6 +17,9 @@
 //     the weight-gradient (dW = dY^T X) and data-gradient (dX = dY W) contractions need, so no transposed
 //     copies of activations or weights are ever materialised.
 //   * split-K (fp32 red.add epilogue) for the weight-gradient shapes whose output has too few tiles for 148 SMs.
+//   * work units are not dealt round robin: the producer draws them from a global counter (see "dynamic tile feed"
+//     below), so a grid that loses SMs to a concurrent kernel (the gradient all-reduce) slows down in proportion
+//     instead of waiting for its unlucky CTAs.
 #include "common.cuh"
 
 namespace penroz {
@@ -122,11 +125,6 @@ __device__ __forceinline__ void feed_retire(int slot, unsigned int drawers) {
     }
 }
 
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_enc, uint32_t sbo_enc) {
-    // cute::UMMA::SmemDescriptor: start[0,14) | LBO[16,30) | SBO[32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
-    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)lbo_enc << 16) | ((uint64_t)sbo_enc << 32) |
-           (1ull << 46) | (2ull << 61);
-}
 
 
 // ------------------------------------------------------------------ epilogue helpers (one warp, one 32x32 chunk)
