@@ -16,6 +16,8 @@
 // (S, dP, dV += P^T dO, dK += dS^T Q, dQ_i = dS K) with dV/dK accumulating in TMEM and dQ reduced across key tiles
 // with fp32 red.add into a scratch buffer, converted to bf16 by a small finishing kernel.
 #include "common.cuh"
+#include <stdlib.h>
+#include <string.h>
 
 namespace penroz {
 
@@ -51,6 +53,12 @@ struct AttnFwdSmem {
 
 __device__ __forceinline__ void softmax_pair_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
+// LAZY: the output accumulates in TMEM across key tiles (the PV MMA adds), and a row is rescaled only when its running
+// maximum grows by more than 2^8 -- rare after the first tile -- so the softmax warps neither wait for PV_j nor read
+// O back every tile, and the issuing thread queues S_{j+1} ahead of PV_j (S is free as soon as P_j is written).
+constexpr float kLazyTau = 8.0f;   // log2 units; probabilities stay <= 2^8, far inside bf16 / fp32 range
+
+template <bool LAZY>
 __global__ void __launch_bounds__(320, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __restrict__ out,
                    float* __restrict__ lse, int Tn, int H, float scale_log2e) {
@@ -110,7 +118,56 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
             const uint32_t idO = at_idesc(0, 1, AT_D);
             constexpr uint32_t kHi = desc_hi(64u);
             mbar_wait(q_full, 0);
-            for (int j = 0; j < n_kv; ++j) {
+            auto issue_s = [&]() {
+                const uint32_t q_lo = desc_lo(sQ, 1), k_lo = desc_lo(sK, 1);
+#pragma unroll
+                for (int k4 = 0; k4 < AT_D / 16; ++k4)
+                    umma_bf16(tS, desc_make(q_lo + k4 * 2, kHi), desc_make(k_lo + k4 * 2, kHi), idS, (uint32_t)(k4 != 0));
+                umma_commit(s_full);
+                umma_commit(k_empty);
+            };
+            if (LAZY) {
+                mbar_wait(k_full, 0);
+                tc_fence_after();
+                issue_s();                                               // S_0
+                if (n_kv > 1) {
+                    mbar_wait(k_empty, 0);
+                    mbar_expect_tx(k_full, 16384);
+                    tma_load_2d(sK, &tmQKV, k_full, C + h * AT_D, b * Tn + AT_BN);
+                    mbar_expect_tx(v_full0 + 8, 16384);
+                    tma_load_2d(sbase + AttnFwdSmem::kV0 + 16384, &tmQKV, v_full0 + 8, 2 * C + h * AT_D, b * Tn + AT_BN);
+                }
+                for (int j = 0; j < n_kv; ++j) {
+                    const int s = j & 1;
+                    const uint32_t sV = sbase + AttnFwdSmem::kV0 + s * 16384;
+                    mbar_wait(v_full0 + 8 * s, (uint32_t)((j >> 1) & 1));
+                    mbar_wait(p_ready, (uint32_t)(j & 1));              // P_j in smem, S free, O rescaled if it had to be
+                    tc_fence_after();
+                    if (j + 1 < n_kv) {
+                        mbar_wait(k_full, (uint32_t)((j + 1) & 1));
+                        tc_fence_after();
+                        issue_s();                                       // S_{j+1} ahead of PV_j
+                    }
+                    {
+                        const uint32_t p_lo = desc_lo(sP, 1), v_lo = desc_lo(sV, 512);
+#pragma unroll
+                        for (int k8 = 0; k8 < AT_BN / 16; ++k8)
+                            umma_bf16(tO, desc_make(p_lo + (k8 >> 2) * 1024 + (k8 & 3) * 2, kHi), desc_make(v_lo + k8 * 128, kHi), idO,
+                                      (uint32_t)((j | k8) != 0));     // accumulates across key tiles
+                    }
+                    umma_commit(o_full);
+                    umma_commit(v_empty0 + 8 * s);
+                    if (j + 2 < n_kv) {
+                        mbar_wait(k_empty, (uint32_t)((j + 1) & 1));    // S_{j+1} has consumed K_{j+1}
+                        mbar_expect_tx(k_full, 16384);
+                        tma_load_2d(sK, &tmQKV, k_full, C + h * AT_D, b * Tn + (j + 2) * AT_BN);
+                        mbar_wait(v_empty0 + 8 * s, (uint32_t)((j >> 1) & 1));   // PV_j has consumed V_j
+                        mbar_expect_tx(v_full0 + 8 * s, 16384);
+                        tma_load_2d(sV, &tmQKV, v_full0 + 8 * s, 2 * C + h * AT_D, b * Tn + (j + 2) * AT_BN);
+                    }
+                }
+            }
+            for (int j = 0; !LAZY && j < n_kv; ++j) {
                 const int s = j & 1;
                 const uint32_t sV = sbase + AttnFwdSmem::kV0 + s * 16384;
                 mbar_wait(k_full, (uint32_t)(j & 1));
@@ -188,8 +245,28 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
             mx[half * 128 + r] = mt;
             softmax_pair_sync();
             mt = fmaxf(mt, mx[(half ^ 1) * 128 + r]);
-            const float mn = fmaxf(m, mt * scale_log2e);   // scale > 0: max commutes with the scaling
-            const float corr = ex2_fast(m - mn);           // m = -inf on the first tile -> 0
+            float mn = fmaxf(m, mt * scale_log2e);   // scale > 0: max commutes with the scaling
+            float corr = ex2_fast(m - mn);           // m = -inf on the first tile -> 0
+            if (LAZY) {
+                // keep the stale maximum unless it grew by more than tau; the first tile only sets it (O is overwritten)
+                const bool jump = (j > 0) && (mn - m > kLazyTau);
+                if (j > 0 && !jump) { mn = m; corr = 1.f; }
+                if (j > 0) {
+                    // PV_{j-1} must have finished: it reads the P buffer pass 2 is about to overwrite, and it is what a
+                    // rescale would scale. By now (a whole pass over S later) it normally has; nothing waits here.
+                    mbar_wait(o_full, (uint32_t)((j - 1) & 1));
+                    tc_fence_after();
+                }
+                if (__any_sync(0xffffffffu, jump)) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(tO + lane_addr + half * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) v[k] = __float_as_uint(__uint_as_float(v[k]) * corr);
+                    tmem_st_32x32(tO + lane_addr + half * 32, v);
+                    tmem_st_wait();
+                }
+            }
             float ls = 0.f;
             // pass 2: p = 2^(s*scale*log2e - mn), partial row sum, P -> smem (bf16, swizzled K-major)
 #pragma unroll 1
@@ -221,16 +298,16 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
             fence_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(p_ready);
-            l = l * corr + ls;
+            l = (LAZY && j == 0) ? ls : l * corr + ls;
             m = mn;
-            mbar_wait(o_full, (uint32_t)(j & 1));
-            tc_fence_after();
-            {
+            if (!LAZY || j == n_kv - 1) {
+                mbar_wait(o_full, (uint32_t)(j & 1));
+                tc_fence_after();
                 uint32_t v[32];
                 tmem_ld_32x32(tO + lane_addr + half * 32, v);
                 tmem_ld_wait();
 #pragma unroll
-                for (int k = 0; k < 32; ++k) o[k] = o[k] * corr + __uint_as_float(v[k]);
+                for (int k = 0; k < 32; ++k) o[k] = LAZY ? __uint_as_float(v[k]) : o[k] * corr + __uint_as_float(v[k]);
             }
             tc_fence_before();
         }
@@ -588,13 +665,20 @@ extern "C" int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B,
     int dev = 0;
     cudaGetDevice(&dev);
     if (!((configured.load() >> dev) & 1)) {
-        cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnFwdSmem::kBytes);
+        cudaError_t e = cudaFuncSetAttribute(attn_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnFwdSmem::kBytes);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(attn_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnFwdSmem::kBytes);
         if (e != cudaSuccess) { set_error("attn_fwd_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
         configured.fetch_or(1 << dev);
     }
     dim3 grid((T + AT_BM - 1) / AT_BM, H, B);
     const float scale_log2e = (1.0f / sqrtf((float)D)) * 1.44269504088896340736f;
-    attn_fwd_tc_kernel<<<grid, 320, AttnFwdSmem::kBytes, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, scale_log2e);
+    // PENROZ_ATTN_FWD=classic: rescale and read the output back every key tile (the first version of this kernel)
+    static const bool lazy = !(getenv("PENROZ_ATTN_FWD") && !strcmp(getenv("PENROZ_ATTN_FWD"), "classic"));
+    if (lazy)
+        attn_fwd_tc_kernel<true><<<grid, 320, AttnFwdSmem::kBytes, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, scale_log2e);
+    else
+        attn_fwd_tc_kernel<false><<<grid, 320, AttnFwdSmem::kBytes, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, lse, T, H, scale_log2e);
     count_launch();
     return check_launch("attn_fwd_tc");
 }

@@ -250,6 +250,45 @@ def test_attention_tensor_core(dev, B, T, H, monkeypatch):
         assert rel_err(dqkv[..., sl], ref_d[..., sl]) < 2e-2, name
 
 
+@pytest.mark.parametrize("mode", ["lazy", "classic"])
+def test_attention_forward_with_growing_scores(dev, mode, monkeypatch):
+    """Scores that keep growing along the sequence, so the running row maximum jumps by far more than the 2^8 the
+    forward kernel tolerates before it rescales its TMEM accumulator -- and a plain random case where it never does.
+    Both schedules (output accumulated in TMEM with lazy rescale / read back every tile) against SDPA in fp32."""
+    import subprocess, sys, os, textwrap
+    code = textwrap.dedent("""
+        import sys, torch, torch.nn.functional as F
+        sys.path.insert(0, "penr-oz-neural-network-v3-torch-ddp_b200")
+        from penroz import ops
+        torch.manual_seed(3)
+        B, T, H, D = 2, 1024, 3, 64
+        C = H * D
+        for ramp in (0.0, 1.0):
+            qkv = torch.randn(B, T, 3 * C, device="cuda")
+            grow = 1.0 + ramp * 6.0 * torch.arange(T, device="cuda").float().view(1, T, 1) / T       # keys get up to 7x larger
+            qkv[:, :, C:2 * C] *= grow
+            qkv = qkv.bfloat16()
+            q, k, v = [t.view(B, T, H, D).transpose(1, 2).float() for t in qkv.split(C, dim=2)]
+            ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, C)
+            out, lse = ops.attn_fwd(qkv, H)
+            err = ((out.float() - ref).norm() / ref.norm()).item()
+            ref_lse = torch.logsumexp((q @ k.transpose(-1, -2) / 8.0).masked_fill(
+                torch.ones(T, T, device="cuda").triu(1).bool(), float("-inf")), dim=-1)
+            lerr = (lse - ref_lse).abs().max().item()
+            print("ramp", ramp, "rel err", err, "lse err", lerr)
+            assert err < 1e-2 and lerr < 2e-2, (ramp, err, lerr)
+        print("OK")
+    """)
+    env = dict(os.environ)
+    if mode == "classic":
+        env["PENROZ_ATTN_FWD"] = "classic"
+    else:
+        env.pop("PENROZ_ATTN_FWD", None)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "OK" in r.stdout, r.stdout[-1500:] + r.stderr[-3000:]
+
+
 # ------------------------------------------------------------------ cross entropy, AdamW, grad norm
 @pytest.mark.parametrize("V,ld,dtype", [(65, 65, torch.float32), (50257, 50304, torch.bfloat16), (50257, 50304, torch.float32),
                                          (1000, 1000, torch.bfloat16)])
