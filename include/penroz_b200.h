@@ -194,7 +194,7 @@ int penroz_argmax_rows(const void* x, long long ld, int rows, int V, long long* 
  * at position `pos`, every block (LN, QKV, paged K/V append at `pos`, split-KV attention over pos+1 keys, proj+residual,
  * LN, fc+GELU, proj2+residual), final LN, LM head into logits_out [B,V] (model dtype) and, when argmax_out is not NULL,
  * the greedy token ids. `layers` is a HOST array; every pointer inside it is a device pointer.
- * For B <= 16 the step runs as five launches per block (decode_fused.cu): LayerNorm, bias, GELU, residual and the K/V
+ * For B <= 8 the step runs as five launches per block (decode_fused.cu): LayerNorm, bias, GELU, residual and the K/V
  * page write ride in the prologue / epilogue of weight-streaming GEMV kernels, the split-KV attention merges its
  * partials inside a thread-block cluster, and consecutive launches overlap through programmatic dependent launch;
  * larger batches take one kernel per op with tensor-core GEMMs. Same results up to summation order. */

@@ -340,7 +340,8 @@ namespace penroz {
 // y = epi(x W^T + b): skinny kernel for few rows, tensor-core / FP32-pipe GEMM otherwise. epi: 0 store, 1 gelu, 2 resid
 static int decode_linear(const void* x, const void* W, const void* b, void* out, const void* aux, int M, int N, int K,
                          int epi, int tanh_, int dtype, void* scratch_pre, void* stream) {
-    const int skinny_rows = (dtype == F32) ? 64 : 16;
+    static const int bf16_rows = getenv("PENROZ_DECODE_SKINNY_ROWS") ? atoi(getenv("PENROZ_DECODE_SKINNY_ROWS")) : 8;
+    const int skinny_rows = (dtype == F32) ? 64 : bf16_rows;
     if (M <= skinny_rows)
         return penroz_skinny_linear(x, K, W, K, b, out, N, aux, N, nullptr, 0, M, N, K, epi, tanh_, dtype, stream);
     if (dtype == BF16) {

@@ -1,4 +1,4 @@
-// Small-batch (B <= 16) single-token step: five launches per transformer block instead of nine, every one a
+// Small-batch (B <= 8) single-token step: five launches per transformer block instead of nine, every one a
 // weight-streaming kernel sized for HBM latency rather than for FLOPs.
 //
 // At B = 1 a GPT-2 124M token reads 326 MB of weights (51 us at the measured 6.4 TB/s) but each Linear is only
@@ -582,9 +582,9 @@ static int fused_splits(int B, int H, int t_len) {
     return want < 1 ? 1 : want;
 }
 
-// small batch (measured: faster than the tensor-core path up to B = 16, slower at 64) and a head dimension the lane layout of attn_decode_split2_kernel covers
+// small batch (measured at 124M bf16: faster than the tensor-core path at B = 8, slower at B = 16) and a head dimension the lane layout of attn_decode_split2_kernel covers
 static int small_batch_limit() {   // PENROZ_DECODE_SMALL_MAX overrides the largest batch the fused step takes
-    static const int v = getenv("PENROZ_DECODE_SMALL_MAX") ? atoi(getenv("PENROZ_DECODE_SMALL_MAX")) : 16;
+    static const int v = getenv("PENROZ_DECODE_SMALL_MAX") ? atoi(getenv("PENROZ_DECODE_SMALL_MAX")) : 8;
     return v;
 }
 bool decode_small_supported(int B, int C, int H, int dtype) {
