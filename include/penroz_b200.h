@@ -205,6 +205,15 @@ typedef struct penroz_gpt2_layer_t {
     int gelu_tanh, ffn;
 } penroz_gpt2_layer_t;
 size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F, int t_len_max);
+/* The prompt pass that starts a generation (neural_net_model.py:387-390 with an empty cache): all S positions through
+ * every block with K/V appended at positions 0..S-1, final LayerNorm + LM head on the last position of each sequence
+ * only; logits_out [B,V]. Same kernels as the per-op entry points, one host call. */
+size_t penroz_gpt2_prefill_workspace_bytes(int B, int S, int C, int F);
+int penroz_gpt2_prefill(const long long* tokens, const void* wte, const void* wpe, const penroz_gpt2_layer_t* layers,
+                        int n_layer, const void* lnf_w, const void* lnf_b, float lnf_eps, const void* head_w,
+                        const void* head_b, const int* block_table, int max_pages, int B, int S, int C, int H, int V,
+                        int dtype, void* workspace, size_t workspace_bytes, void* logits_out, long long* argmax_out,
+                        int* err_flag, void* stream);
 int penroz_gpt2_decode_step(const long long* tokens, const void* wte, const void* wpe,
                             const penroz_gpt2_layer_t* layers, int n_layer, const void* lnf_w, const void* lnf_b,
                             float lnf_eps, const void* head_w, const void* head_b, const int* block_table,

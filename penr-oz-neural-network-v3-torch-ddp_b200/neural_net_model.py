@@ -511,6 +511,8 @@ class NeuralNetworkModel(nn.Module):
             greedy_ids = None
             if model_input.shape[1] == 1:      # incremental step: one native call enqueues the whole token step
                 logits, greedy_ids = engine.decode_step(model_input, offset, kv_cache)
+            elif offset == 0 and os.environ.get("PENROZ_PREFILL", "native") == "native":
+                logits, greedy_ids = engine.prefill(model_input, kv_cache)      # the whole prompt pass, one native call
             else:
                 logits, _, _ = engine.forward_infer(model_input.contiguous(), None, pos_offset=offset, kv=kv_cache,
                                                     last_only=True)

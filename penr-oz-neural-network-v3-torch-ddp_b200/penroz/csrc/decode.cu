@@ -421,3 +421,72 @@ extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte,
     if (argmax_out) rc = penroz_argmax_rows(logits_out, V, B, V, argmax_out, dtype, stream);
     return rc;
 }
+
+// ------------------------------------------------------------------ whole prompt pass (prefill), enqueued from C++
+// The first decode iteration runs the full prompt through the model with an empty cache (neural_net_model.py:387-390,
+// 250-258 with the cache branch of neural_net_layers.py:83-92 appending S tokens) and keeps only the last position's
+// logits. Same kernels as the per-op entry points -- tensor-core GEMMs, tcgen05 flash attention, paged K/V append for
+// all S positions -- enqueued with ONE host call; LayerNorm + LM head run on the B last rows only.
+extern "C" {
+int penroz_attn_fwd_simt(const void*, void*, float*, int, int, int, int, int, void*);
+int penroz_attn_fwd_tc(const void*, void*, float*, int, int, int, int, void*);
+}
+
+extern "C" size_t penroz_gpt2_prefill_workspace_bytes(int B, int S, int C, int F) {
+    const size_t M = (size_t)B * S;
+    // x, x', LN out, qkv, attention out, GELU out, pre-activation, last rows (fp32-sized; bf16 uses half)
+    return (M * ((size_t)3 * C + 3 * C + C + 2 * (size_t)F) + (size_t)B * C) * 4 + 10 * 256;
+}
+
+extern "C" int penroz_gpt2_prefill(const long long* tokens, const void* wte, const void* wpe,
+                                   const penroz_gpt2_layer_t* layers, int n_layer, const void* lnf_w, const void* lnf_b,
+                                   float lnf_eps, const void* head_w, const void* head_b, const int* block_table,
+                                   int max_pages, int B, int S, int C, int H, int V, int dtype, void* workspace,
+                                   size_t workspace_bytes, void* logits_out, long long* argmax_out, int* err_flag,
+                                   void* stream) {
+    PENROZ_REQUIRE(B > 0 && S > 0 && C > 0 && H > 0 && V > 0 && n_layer > 0, "gpt2_prefill: bad shape");
+    PENROZ_REQUIRE(C % H == 0, "gpt2_prefill: n_embd %d not divisible by %d heads", C, H);
+    PENROZ_REQUIRE(dtype == F32 || dtype == BF16, "gpt2_prefill: bad dtype %d", dtype);
+    PENROZ_REQUIRE((long long)B * S < (1LL << 31), "gpt2_prefill: too many rows");
+    int F = 0;
+    for (int l = 0; l < n_layer; ++l) F = layers[l].ffn > F ? layers[l].ffn : F;
+    PENROZ_REQUIRE(workspace && workspace_bytes >= penroz_gpt2_prefill_workspace_bytes(B, S, C, F),
+                   "gpt2_prefill: workspace too small");
+    const int D = C / H, M = B * S;
+    const size_t es = dtype == F32 ? 4 : 2;
+    uint8_t* w = (uint8_t*)workspace;
+    auto carve = [&](size_t elems) { void* p = w; w += ((elems * es + 255) / 256) * 256; return p; };
+    void* xa = carve((size_t)M * C);
+    void* xb = carve((size_t)M * C);
+    void* ln = carve((size_t)M * C);
+    void* qkv = carve((size_t)M * 3 * C);
+    void* att = carve((size_t)M * C);
+    void* g = carve((size_t)M * F);
+    void* hpre = carve((size_t)M * F);
+    void* last = carve((size_t)B * C);
+    const bool tc_attn = (dtype == BF16) && D == 64 && !(getenv("PENROZ_ATTENTION") && !strcmp(getenv("PENROZ_ATTENTION"), "simt"));
+    int rc = penroz_embed_fwd(tokens, wte, wpe, xa, B, S, C, V, 0, dtype, dtype, err_flag, stream);
+    if (rc) return rc;
+    void *x = xa, *xo = xb;
+    for (int l = 0; l < n_layer; ++l) {
+        const penroz_gpt2_layer_t& L = layers[l];
+        if ((rc = penroz_layernorm_fwd(x, L.ln1_w, L.ln1_b, ln, nullptr, nullptr, M, C, L.ln1_eps, dtype, dtype, dtype, stream))) return rc;
+        if ((rc = decode_linear(ln, L.qkv_w, L.qkv_b, qkv, nullptr, M, 3 * C, C, 0, 0, dtype, nullptr, stream))) return rc;
+        if ((rc = penroz_kv_append(qkv, L.kv_pool, block_table, max_pages, B, S, H, D, 0, dtype, stream))) return rc;
+        if (tc_attn) rc = penroz_attn_fwd_tc(qkv, att, nullptr, B, S, H, D, stream);
+        else rc = penroz_attn_fwd_simt(qkv, att, nullptr, B, S, H, D, dtype, stream);
+        if (rc) return rc;
+        if ((rc = decode_linear(att, L.proj_w, L.proj_b, xo, x, M, C, C, 2, 0, dtype, nullptr, stream))) return rc;
+        if ((rc = penroz_layernorm_fwd(xo, L.ln2_w, L.ln2_b, ln, nullptr, nullptr, M, C, L.ln2_eps, dtype, dtype, dtype, stream))) return rc;
+        if ((rc = decode_linear(ln, L.fc_w, L.fc_b, g, nullptr, M, L.ffn, C, 1, L.gelu_tanh, dtype, hpre, stream))) return rc;
+        if ((rc = decode_linear(g, L.proj2_w, L.proj2_b, x, xo, M, C, L.ffn, 2, 0, dtype, nullptr, stream))) return rc;
+    }
+    // final LayerNorm and LM head on the last position of every sequence only
+    for (int b = 0; b < B; ++b) {
+        const uint8_t* src = (const uint8_t*)x + ((size_t)b * S + (S - 1)) * C * es;
+        if ((rc = penroz_layernorm_fwd(src, lnf_w, lnf_b, (uint8_t*)last + (size_t)b * C * es, nullptr, nullptr, 1, C, lnf_eps, dtype, dtype, dtype, stream))) return rc;
+    }
+    if ((rc = decode_linear(last, head_w, head_b, logits_out, nullptr, B, V, C, 0, 0, dtype, nullptr, stream))) return rc;
+    if (argmax_out) rc = penroz_argmax_rows(logits_out, V, B, V, argmax_out, dtype, stream);
+    return rc;
+}

@@ -213,6 +213,41 @@ class Gpt2Engine:
         return logits, ids
 
     @torch.no_grad()
+    def prefill(self, tokens, kv):
+        """The prompt pass of a generation ([B,S] tokens, empty paged cache) through penroz_gpt2_prefill: one host call
+        enqueues every kernel, K/V of all S positions land in the pages, LayerNorm + LM head run on the last position
+        only. Returns (logits [B,1,V], greedy ids [B,1])."""
+        pl = self.plan
+        B, S = tokens.shape
+        C, H, V = pl.n_embd, pl.n_head, pl.vocab
+        if S > pl.block_size:
+            raise IndexError(f"position {S} exceeds the position table ({pl.block_size})")
+        store = kv._paged
+        if store.length != 0:
+            raise PenrozError("multi-token append onto a non-empty KV cache is not part of the decode path")
+        store.ensure_pages(S)
+        layers = self._native_layers(kv)
+        F = max(b.fc.out_features for b in pl.blocks)
+        need = ops.lib().gpt2_prefill_workspace_bytes(B, S, C, F)
+        ws = getattr(store, "prefill_ws", None)
+        if ws is None or ws.numel() < need:
+            ws = store.prefill_ws = torch.empty(need, device=self.device, dtype=torch.uint8)
+        dt = pl.wte.weight.dtype
+        logits = torch.empty((B, 1, V), device=self.device, dtype=dt)
+        ids = torch.empty((B, 1), device=self.device, dtype=torch.int64)
+        self._err_flag.zero_()
+        lnf_b = None if pl.lnf.bias is None else pl.lnf.bias.data_ptr()
+        head_b = None if pl.head.bias is None else pl.head.bias.data_ptr()
+        ops.lib().gpt2_prefill(tokens.contiguous().data_ptr(), pl.wte.weight.data_ptr(), pl.wpe.weight.data_ptr(),
+                               layers, pl.n_layer, pl.lnf.weight.data_ptr(), lnf_b, pl.lnf.eps,
+                               pl.head.weight.data_ptr(), head_b, store.table_dev.data_ptr(), store.max_pages, B, S, C,
+                               H, V, ops.dt(pl.wte.weight), ws.data_ptr(), ws.numel(), logits.data_ptr(),
+                               ids.data_ptr(), self._err_flag.data_ptr(), ops.stream())
+        kv.account_tokens(S, 2 * B * S * C * logits.element_size(), pl.n_layer)
+        kv.commit(S)
+        return logits, ids
+
+    @torch.no_grad()
     def forward_infer(self, idx, targets=None, pos_offset=0, kv=None, last_only=False, collect=False):
         """Forward in the parameter dtype, no autograd. Returns (logits [B,S|1,V], loss|None, activations|None).
 

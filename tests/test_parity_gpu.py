@@ -310,3 +310,41 @@ def test_forward_under_autograd_on_cuda(env, golden):
     m2.train_model("synth65", 0, 2, 16, 64, 16)
     assert float(m2.optimizer.state_dict()["state"][0]["step"]) == 7.0
     assert float(m2.optimizer.state_dict()["state"][27]["step"]) == 7.0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,S", [(1, 70), (3, 129)])
+def test_native_prefill_matches_per_op_prefill(env, dtype, B, S):
+    """penroz_gpt2_prefill (the whole prompt pass in one native call, LayerNorm + LM head on the last position only)
+    against the per-op forward over the same prompt: last-position logits, greedy ids and every cached K/V page."""
+    from kv_cache import KVCache
+    m = build_gpt(f"pre124_{B}_{S}_{dtype}".replace(".", "_"), 2, 12, 768, 1024, 50257)
+    if dtype != torch.float32:
+        m.to(dtype=dtype)
+    m.to("cuda")
+    eng, pl = m._engine(), m._plan
+    prompt = torch.randint(0, 50257, (B, S), generator=torch.Generator().manual_seed(S)).to(env)
+
+    def fresh():
+        kv = KVCache(pl.n_layer)
+        kv.paged(B, pl.n_head, pl.head_dim, pl.wte.weight.dtype, env, capacity_hint=1024)
+        return kv
+    kv_a, kv_b = fresh(), fresh()
+    with torch.inference_mode():
+        la, ids = eng.prefill(prompt, kv_a)
+        lb, _, _ = eng.forward_infer(prompt, None, pos_offset=0, kv=kv_b, last_only=True)
+    tol = 2e-4 if dtype == torch.float32 else 6e-2
+    la, lb = la.float(), lb.float()
+    assert la.shape == lb.shape == (B, 1, 50257)
+    assert (la - lb).abs().max().item() <= tol * max(1.0, lb.abs().max().item())
+    assert torch.equal(ids.view(-1), la.view(B, -1).argmax(dim=-1))
+    assert kv_a.seq_len() == kv_b.seq_len() == S and kv_a.metrics.total_entries == kv_b.metrics.total_entries
+    sa, sb = kv_a._paged, kv_b._paged
+    assert torch.equal(sa.table_host, sb.table_host)
+    for layer in range(pl.n_layer):
+        for b in range(B):
+            for pg in range((S + 63) // 64):
+                used = min(64, S - 64 * pg)
+                page = int(sa.table_host[b, pg])
+                ka, kb = sa.pools[layer][page, :, :, :used].float(), sb.pools[layer][page, :, :, :used].float()
+                assert (ka - kb).abs().max().item() <= tol * max(1.0, kb.abs().max().item())
