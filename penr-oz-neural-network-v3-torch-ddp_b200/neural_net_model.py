@@ -541,15 +541,17 @@ class NeuralNetworkModel(nn.Module):
             return torch.multinomial(probs.float().cpu(), num_samples=1).to(probs.device)
         return torch.multinomial(probs.float(), num_samples=1)
 
-    def _token_stream(self, input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink):
+    def _token_stream(self, input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink,
+                      emit=True):
         """Shared decode loop: yields each new token id (row 0) and leaves the full context in sink[0]. A model shared
         through the residency cache is held exclusively until the stream ends (generation attaches its KV cache to
         the layers)."""
         with _Exclusive(self):
             yield from self._token_stream_locked(input_context, block_size, max_new_tokens, temperature, top_k,
-                                                 stop_token, sink)
+                                                 stop_token, sink, emit)
 
-    def _token_stream_locked(self, input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink):
+    def _token_stream_locked(self, input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink,
+                             emit=True):
         context, softmax_layer = self._prepare_generation(input_context, max_new_tokens, temperature, top_k)
         cache, positions = self._attach_kv_cache()
         try:
@@ -558,6 +560,8 @@ class NeuralNetworkModel(nn.Module):
                                                 positions)
                 context = torch.cat((context, nxt), dim=1)
                 sink[0] = context
+                if not emit:
+                    continue        # nobody looks at this token before the end: no device->host read, the host runs ahead
                 token = nxt[0].item()
                 yield token
                 if stop_token is not None and token == stop_token:
@@ -572,7 +576,10 @@ class NeuralNetworkModel(nn.Module):
     def generate_tokens(self, input_context: list, block_size: int, max_new_tokens: int,
                         temperature=1.0, top_k: int | None = None, stop_token: int | None = None) -> list:
         sink = [None]
-        for _ in self._token_stream(input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink):
+        # greedy decoding without a stop token needs no token on the host until the end (sampling draws on the host)
+        emit = not (temperature == 0.0 and stop_token is None)
+        for _ in self._token_stream(input_context, block_size, max_new_tokens, temperature, top_k, stop_token, sink,
+                                    emit=emit):
             pass
         if sink[0] is None:  # max_new_tokens == 0
             sink[0] = torch.tensor(input_context, dtype=torch.long)
