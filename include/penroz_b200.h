@@ -55,7 +55,10 @@ int penroz_query(int* cc_major, int* cc_minor, int* sm_count);
  * Replaces torch nn.Linear forward and its autograd backward (modules built at mappers.py:21,156,158,163,165,172;
  * run at neural_net_model.py:250-258; backward at neural_net_model.py:650-653).
  * a_layout/b_layout: 0 = operand stored [rows, K] (K contiguous), 1 = stored [K, rows] (rows contiguous).
- * penroz_gemm_bf16: tcgen05.mma (TMEM accumulators) fed by TMA; bias is bf16. penroz_gemm_f32: FP32 FMA pipes. */
+ * penroz_gemm_bf16: tcgen05.mma (TMEM accumulators) fed by TMA; bias is bf16. penroz_gemm_f32: FP32 FMA pipes.
+ * penroz_gemm_bf16 draws its output tiles from a counter pair inside the library (1024 pairs, one dealt per call,
+ * reset by the call's last CTA): calls on any number of streams or threads are independent, but ONE captured launch
+ * replayed concurrently with itself would share its pair -- replay such a graph on one stream at a time. */
 int penroz_gemm_bf16(const void* A, long long lda, int a_layout, const void* B, long long ldb, int b_layout, int M,
                      int N, int K, int epilogue, const void* bias, void* out, long long ldo, void* out2,
                      long long ldo2, const void* aux, long long ldaux, int flags, void* stream);
