@@ -43,6 +43,25 @@ __global__ void kv_append_kernel(const T* __restrict__ qkv, T* __restrict__ pool
     }
 }
 
+// same, 16 bytes per thread: a thread moves VN consecutive head-dimension elements of one (row, k|v, head)
+template <typename T>
+__global__ void kv_append_vec_kernel(const T* __restrict__ qkv, T* __restrict__ pool, const int* __restrict__ bt,
+                                     int max_pages, int B, int S, int H, int D, int t0) {
+    constexpr int VN = Vec16<T>::N;
+    const int C = H * D, dv = D / VN, cv = C / VN;
+    const size_t total = (size_t)B * S * 2 * cv;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int c = (int)(e % cv);
+        const int kv = (int)((e / cv) % 2);
+        const size_t row = e / (2 * (size_t)cv);          // b * S + s
+        const int s = (int)(row % S), b = (int)(row / S);
+        const int h = c / dv, d = (c - h * dv) * VN;
+        Vec16<T> v;
+        v.load(qkv + row * 3 * C + (size_t)(1 + kv) * C + (size_t)c * VN);
+        v.store(const_cast<T*>(page_row(pool, bt, max_pages, b, kv, H, h, D, t0 + s)) + d);
+    }
+}
+
 // partial attention of one query row against keys [k0, k1) of its sequence; part layout [B][H][splits][D + 2]
 template <typename T>
 __global__ void __launch_bounds__(128)
@@ -222,11 +241,15 @@ extern "C" int penroz_kv_append(const void* qkv, void* pool, const int* block_ta
     PENROZ_REQUIRE(B > 0 && S > 0 && H > 0 && D > 0 && t0 >= 0, "kv_append: bad shape");
     PENROZ_REQUIRE((t0 + S + KV_PAGE - 1) / KV_PAGE <= max_pages, "kv_append: position %d exceeds the block table (%d pages)", t0 + S, max_pages);
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t total = (size_t)B * S * 2 * H * D;
+    const int vn = dtype == F32 ? 4 : 8;
+    const bool vec = (D % vn == 0) && (((uintptr_t)qkv | (uintptr_t)pool) % 16 == 0);
+    const size_t total = (size_t)B * S * 2 * H * D / (vec ? vn : 1);
     size_t g = (total + 255) / 256;
     const size_t cap = (size_t)num_sms() * 16;
     const int grid = (int)(g > cap ? cap : g);
-    if (dtype == F32) kv_append_kernel<float><<<grid, 256, 0, st>>>((const float*)qkv, (float*)pool, block_table, max_pages, B, S, H, D, t0);
+    if (vec && dtype == F32) kv_append_vec_kernel<float><<<grid, 256, 0, st>>>((const float*)qkv, (float*)pool, block_table, max_pages, B, S, H, D, t0);
+    else if (vec && dtype == BF16) kv_append_vec_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)qkv, (__nv_bfloat16*)pool, block_table, max_pages, B, S, H, D, t0);
+    else if (dtype == F32) kv_append_kernel<float><<<grid, 256, 0, st>>>((const float*)qkv, (float*)pool, block_table, max_pages, B, S, H, D, t0);
     else if (dtype == BF16) kv_append_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)qkv, (__nv_bfloat16*)pool, block_table, max_pages, B, S, H, D, t0);
     else { set_error("kv_append: bad dtype %d", dtype); return PENROZ_ERR_ARG; }
     count_launch();
