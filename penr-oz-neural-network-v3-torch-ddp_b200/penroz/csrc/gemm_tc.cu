@@ -988,6 +988,9 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     }
     if (flags & 4) { bn = 128; pair = false; }
     if (flags & 8) { bn = 256; pair = pair_ok; }
+    // a single 128-row tile of activations (decode at batch <= 128): the kernel is a weight stream and every CTA pulls
+    // BN rows of W, so narrower tiles = more CTAs pulling in parallel
+    if (!(flags & 12) && M <= 128 && epilogue != EPI_ACCUM_F32 && N > 64 && ceil_div(N, 128) * 2 <= sms) { bn = 64; pair = false; }
     p.tiles_m = pair ? (M + 2 * BM - 1) / (2 * BM) : tiles_m;
     p.tiles_n = (N + bn - 1) / bn;
     p.kb_total = (K + BK - 1) / BK;
@@ -1021,5 +1024,6 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     const int units = p.tiles_m * p.tiles_n * p.splits;
     const int grid = min(units, sms);
     if (bn == 256) return dispatch_epi<256>(epilogue, tmA, tmB, p, grid, st);
+    if (bn == 64) return dispatch_epi<64>(epilogue, tmA, tmB, p, grid, st);
     return dispatch_epi<128>(epilogue, tmA, tmB, p, grid, st);
 }
