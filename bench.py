@@ -51,7 +51,7 @@ def measured_peaks():
 
 def ncu_traffic_per_launch(family: str):
     """Mean DRAM bytes per launch of a kernel family, from the committed ncu launch list of this same command."""
-    path = os.path.join(ROOT, "profiles", "r01c_ncu_launch_list_step.json")
+    path = os.path.join(ROOT, "profiles", "r01f_ncu_launch_list_step.json")
     try:
         fams = json.load(open(path))["families"]
     except Exception:
@@ -373,7 +373,7 @@ def run_ours(args):
         peak = peaks["bf16_tflops_sustained"]
         roofline = {"kernel": name, "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                     "frac": achieved / peak, "traffic": ncu_traffic_per_launch(name),
-                    "traffic_source": "profiles/r01c_ncu_launch_list_step.json (dram__bytes_read+write per launch, family mean)",
+                    "traffic_source": "profiles/r01f_ncu_launch_list_step.json (dram__bytes_read+write per launch, family mean)",
                     "peak_source": f"{which} (sustained: kernel timed inside a long step)",
                     "share_of_step": d["ms"] / step_ms, "launches_per_step": d["launches"],
                     "families_ms": {k: round(v["ms"], 3) for k, v in fam.items()}, "instrumented_step_ms": step_ms}
