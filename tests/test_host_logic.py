@@ -275,3 +275,36 @@ def test_model_residency_cache(monkeypatch):
     monkeypatch.setenv("PENROZ_MODEL_CACHE", "0")
     assert nnm.NeuralNetworkModel.deserialize("res_b") is not nnm.NeuralNetworkModel.deserialize("res_b")
     nnm._RESIDENT.clear()
+
+
+def test_resident_model_serialises_concurrent_requests(monkeypatch):
+    """Two request threads that deserialize the same resident model and generate at once (the service's threadpool,
+    main.py:421-436) must each get the tokens a lone request gets: generation attaches its KV cache to the shared
+    layers, so the residency entry's lock has to keep the calls apart."""
+    import threading
+    import neural_net_model as nnm
+    scratch_cwd()
+    monkeypatch.setenv("PENROZ_MODEL_CACHE", "1")
+    nnm._RESIDENT.clear()
+    build_gpt("res_t", 2, 2, 32, 32, 17).serialize()
+    prompts = [[[1, 2, 3, 4]], [[9, 8, 7]], [[5, 5, 5, 5, 5]], [[2, 11, 3]]]
+    alone = [nnm.NeuralNetworkModel.deserialize("res_t").generate_tokens(p, 32, 20, temperature=0.0) for p in prompts]
+    got, errors = [None] * len(prompts), []
+
+    def request(i):
+        try:
+            model = nnm.NeuralNetworkModel.deserialize("res_t")
+            got[i] = list(model.generate_tokens_stream(prompts[i], 32, 20, temperature=0.0))
+        except Exception as e:          # noqa: BLE001 - reported below
+            errors.append(repr(e))
+    for _ in range(3):
+        threads = [threading.Thread(target=request, args=(i,)) for i in range(len(prompts))]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        assert not errors, errors
+        for i, p in enumerate(prompts):
+            assert got[i] == alone[i][len(p[0]):], i
+    assert len(nnm._RESIDENT) == 1
+    nnm._RESIDENT.clear()
