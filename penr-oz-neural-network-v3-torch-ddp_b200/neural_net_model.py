@@ -66,8 +66,13 @@ MODELS_FOLDER = "models"
 # models resident in the process. An entry is valid while the cached file is byte-for-byte the one it was loaded from
 # (same mtime_ns and size), so a training process rewriting the file invalidates it; the on-disk format is unchanged.
 # Those requests only read the model, but generation attaches its KV cache to the layers, so calls that run the model
-# take the entry's lock. PENROZ_MODEL_CACHE=0|1 (default: on when a GPU is visible), PENROZ_MODEL_CACHE_SIZE (2).
-_RESIDENT: "OrderedDict[str, tuple]" = OrderedDict()      # cached-file path -> (mtime_ns, size, model, RLock)
+# take the model's run lock. The lock lives on the model object (a caller may still hold the object after the LRU has
+# dropped its entry) and is a plain non-reentrant Lock: the service drives generate_tokens_stream through Starlette's
+# StreamingResponse, one threadpool dispatch per next() (main.py:427-431), so the thread that finishes or closes the
+# stream need not be the one that started it -- an RLock could not be released there, and would let a second request
+# scheduled onto the owner's thread walk straight in. PENROZ_MODEL_CACHE=0|1 (default: on when a GPU is visible),
+# PENROZ_MODEL_CACHE_SIZE (2).
+_RESIDENT: "OrderedDict[str, tuple]" = OrderedDict()      # cached-file path -> (mtime_ns, size, model)
 _RESIDENT_GUARD = threading.Lock()
 
 
@@ -84,13 +89,11 @@ def _file_stamp(path: str):
 
 
 class _Exclusive:
-    """Context manager: the resident entry's lock when `model` is shared through the residency cache, else nothing."""
+    """Context manager: the model's run lock when `model` was handed out by the residency cache (and so may be shared
+    between request threads), else nothing. Acquire and release may happen on different threads."""
 
     def __init__(self, model):
-        key = model.__dict__.get("_resident_key")
-        with _RESIDENT_GUARD:
-            entry = _RESIDENT.get(key) if key else None
-        self.lock = entry[3] if entry is not None and entry[2] is model else None
+        self.lock = model.__dict__.get("_run_lock")
 
     def __enter__(self):
         if self.lock is not None:
@@ -206,7 +209,7 @@ class NeuralNetworkModel(nn.Module):
             entry = _RESIDENT.get(shm_path)
             if entry is not None:
                 if entry[2] is self:        # the file now holds exactly this object's state: keep it resident
-                    _RESIDENT[shm_path] = _file_stamp(shm_path) + (self, entry[3])
+                    _RESIDENT[shm_path] = _file_stamp(shm_path) + (self,)
                 else:
                     del _RESIDENT[shm_path]
         if chatty:
@@ -262,8 +265,9 @@ class NeuralNetworkModel(nn.Module):
             log.info(f"Model {model_id} is fully loaded")
         if resident and _file_stamp(shm_path) == stamp:       # not rewritten while it was being read
             model.__dict__["_resident_key"] = shm_path
+            model.__dict__["_run_lock"] = threading.Lock()
             with _RESIDENT_GUARD:
-                _RESIDENT[shm_path] = stamp + (model, threading.RLock())
+                _RESIDENT[shm_path] = stamp + (model,)
                 _RESIDENT.move_to_end(shm_path)
                 keep = max(1, int(os.environ.get("PENROZ_MODEL_CACHE_SIZE", "2")))
                 while len(_RESIDENT) > keep:
@@ -661,6 +665,8 @@ class NeuralNetworkModel(nn.Module):
         else:
             stepper = _TorchStepper(self, device, amp_ctx, amp_scaler)
         stepper.begin()
+        if hasattr(stepper, "warn_if_ranks_will_drift"):
+            stepper.warn_if_ranks_will_drift(num_steps)
         self.layers.training = True
 
         pairs = []
@@ -931,6 +937,16 @@ class _FusedStepper:
                 eng.flat.refresh_shadow()
         else:
             eng.grad_sync = None
+
+    def warn_if_ranks_will_drift(self, num_steps: int):
+        """With accumulation under DDP the reference exchanges gradients in micro-step 0 only (it arms DDP's flag after
+        the forward that reads it): every rank then adds its own later micro-steps and the replicas' weights
+        drift apart, silently. The default reproduces that for parity; say so once, and name the switch."""
+        if (self.engine.grad_sync is not None and num_steps > 1 and self.sync_mode == "reference"
+                and ddp.master_proc()):
+            log.warning(f"DDP with {num_steps} accumulation micro-steps: like the reference, only micro-step 0's gradients "
+                        f"are all-reduced and the ranks' weights will diverge; set PENROZ_ACCUM_SYNC=correct to "
+                        f"exchange the accumulated gradient after the last micro-step instead")
 
     def end(self):
         self.engine.release_workspace()

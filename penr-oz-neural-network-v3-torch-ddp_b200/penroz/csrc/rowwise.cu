@@ -701,6 +701,7 @@ extern "C" size_t penroz_colsum_scratch_bytes(int M, int N) { (void)M; return (s
 extern "C" int penroz_colsum(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype,
                              void* scratch, size_t scratch_bytes, void* stream) {
     PENROZ_REQUIRE(M > 0 && N > 0, "colsum: bad shape");
+    PENROZ_REQUIRE(ld >= N, "colsum: leading dimension %lld is smaller than the row length %d (rows would alias)", ld, N);
     PENROZ_REQUIRE(scratch && scratch_bytes >= penroz_colsum_scratch_bytes(M, N), "colsum: scratch too small");
     cudaStream_t st = (cudaStream_t)stream;
     const int parts = 32;
@@ -772,6 +773,8 @@ extern "C" int penroz_colsum_static(const void* X, long long ld, int M, int N, f
                                     void* stream) {
     PENROZ_REQUIRE(M > 0 && N > 0, "colsum_static: bad shape M=%d N=%d", M, N);
     PENROZ_REQUIRE(X != nullptr && out != nullptr, "colsum_static: null argument");
+    PENROZ_REQUIRE(ld >= N, "colsum_static: leading dimension %lld is smaller than the row length %d (rows would alias)",
+                   ld, N);
     if (N > kStaticColsumMaxCols) {
         set_error("colsum_static: N=%d exceeds the built-in scratch (at most %d columns); use penroz_colsum with "
                   "caller-provided scratch for wider matrices", N, kStaticColsumMaxCols);

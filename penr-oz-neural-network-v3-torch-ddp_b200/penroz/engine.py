@@ -85,7 +85,10 @@ class FlatState:
 
     def adopt_optimizer_state(self, optimizer) -> int:
         """Move any existing AdamW moments into the flat buffers and make optimizer.state[p] views of them.
-        Returns the step count found (0 for a fresh optimizer). The `step` entries share ONE tensor."""
+        Returns the step count found (0 for a fresh optimizer). Every state's `step` is its OWN 0-dim element of one
+        host vector: the fused update sets all of them with a single fill, while a stock torch.optim.AdamW that later
+        loads the saved state (the reference resuming from this checkpoint) increments each parameter's count exactly
+        once per step -- a tensor object shared between the states would be bumped once per parameter."""
         step = 0
         for p in self.params:
             st = optimizer.state.get(p)
@@ -95,9 +98,10 @@ class FlatState:
                     self._view(self.v, p).copy_(st["exp_avg_sq"].to(self.p.device, torch.float32))
                 s = st.get("step", 0)
                 step = max(step, int(s.item()) if torch.is_tensor(s) else int(s))
-        self.step_tensor = torch.tensor(float(step), dtype=torch.float32)
-        for p in self.params:
-            optimizer.state[p] = {"step": self.step_tensor, "exp_avg": self._view(self.m, p),
+        self.step_vec = torch.full((len(self.params),), float(step), dtype=torch.float32)
+        self.step_views = [self.step_vec[i] for i in range(len(self.params))]
+        for i, p in enumerate(self.params):
+            optimizer.state[p] = {"step": self.step_views[i], "exp_avg": self._view(self.m, p),
                                   "exp_avg_sq": self._view(self.v, p)}
         return step
 
@@ -444,11 +448,11 @@ class Gpt2Engine:
             # dW += dlogits^T . lnf (both operands MN-major; TMA zero-fills past column V of the padded chunk)
             ops.gemm(dl, lnf[r0:r1], a_layout=1, b_layout=1, epilogue=EPI_ACCUM_F32, out=g_head, accumulate=True)
             if pl.head.bias is not None:
-                ops.colsum(dl, fl.grad(pl.head.bias), accumulate=True, scratch=self._scratch(M, max(V, 4 * C)))
+                ops.colsum(dl, fl.grad(pl.head.bias), accumulate=True, scratch=self._scratch(M, self._widest()))
         ops.ce_reduce(loss_rows, n_valid, loss)
 
         # ---------------- backward through the blocks
-        scratch = self._scratch(M, max(V, 4 * C))
+        scratch = self._scratch(M, self._widest())
         dx_a, dx_b = buf("dx_a", (M, C), torch.float32), buf("dx_b", (M, C), torch.float32)
         dxb_a = buf("dxb_a", (M, C), torch.bfloat16) if amp else None
         dxb_b = buf("dxb_b", (M, C), torch.bfloat16) if amp else None
@@ -529,7 +533,6 @@ class Gpt2Engine:
         were_none = [p.grad is None for p in self.parameters]
         self.setup_training(use_amp)
         fl = self.flat
-        self._own_step_tensors(True)
         if getattr(fl, "g_pending", None) is None:
             fl.g_pending = torch.zeros_like(fl.g)
         else:
@@ -547,23 +550,24 @@ class Gpt2Engine:
                 p.grad = None
         return loss, kept
 
-    def _own_step_tensors(self, separate: bool):
-        """The fused AdamW keeps ONE `step` tensor shared by every parameter's optimizer state (one fill per step).
-        A stock torch optimizer.step() increments each state's tensor, so before handing the parameters to a caller's
-        own loop every state gets its own tensor; the fused optimizer takes them back (max of the counts)."""
-        if self.optimizer is None or getattr(self, "_steps_separate", False) == separate:
+    def _sync_step_count(self):
+        """A caller's own torch optimizer.step() between fused steps advances the per-parameter `step` entries (each
+        state owns one element of flat.step_vec); the fused update continues from the largest count. States whose
+        `step` object was replaced by foreign code (optimizer.load_state_dict) are read and pointed back."""
+        if self.optimizer is None:
             return
-        states = [self.optimizer.state[p] for p in self.parameters if p in self.optimizer.state]
-        if separate:
-            for st in states:
-                st["step"] = torch.tensor(float(self.step_count), dtype=torch.float32)
-        else:
-            counts = [int(st["step"].item()) if torch.is_tensor(st["step"]) else int(st["step"]) for st in states]
-            self.step_count = max(counts + [self.step_count])
-            self.flat.step_tensor.fill_(float(self.step_count))
-            for st in states:
-                st["step"] = self.flat.step_tensor
-        self._steps_separate = separate
+        fl = self.flat
+        count = max(self.step_count, int(fl.step_vec.max().item()))
+        for i, p in enumerate(self.parameters):
+            st = self.optimizer.state.get(p)
+            if st is None:
+                continue
+            s = st.get("step")
+            if s is not fl.step_views[i]:
+                if s is not None:
+                    count = max(count, int(s.item()) if torch.is_tensor(s) else int(s))
+                st["step"] = fl.step_views[i]
+        self.step_count = count
 
     def backward_pending(self, grad_out):
         fl = self.flat
@@ -575,6 +579,11 @@ class Gpt2Engine:
                 fl.grad(p).zero_()
         fl.rebind_grads()
         ops.axpy_(fl.g, fl.g_pending, grad_out.detach().to(torch.float32).reshape(()).contiguous())
+
+    def _widest(self):
+        """widest matrix whose column sums (bias gradients) go through the scratch: logits, any block's FFN, packed QKV"""
+        pl = self.plan
+        return max(pl.vocab, max(b.fc.out_features for b in pl.blocks), 3 * pl.n_embd)
 
     def _scratch(self, M, widest):
         C, H = self.plan.n_embd, self.plan.n_head
@@ -603,7 +612,7 @@ class Gpt2Engine:
             raise PenrozError("fused AdamW expects the reference's single parameter group (mappers.py:267-274)")
         if grp.get("amsgrad", False) or grp.get("maximize", False):
             raise PenrozError("fused AdamW does not implement amsgrad / maximize")
-        self._own_step_tensors(False)
+        self._sync_step_count()
         self.step_count += 1
         mult = None
         if self.clip_grad_norm > 0.0:
@@ -615,4 +624,4 @@ class Gpt2Engine:
             ops.adamw_flat(fl.p[lo:hi], fl.g[lo:hi], fl.m[lo:hi], fl.v[lo:hi], None if shadow is None else shadow[lo:hi],
                            lr=grp["lr"], betas=grp["betas"], eps=grp["eps"], weight_decay=grp["weight_decay"],
                            step=self.step_count, grad_mult=mult, zero_grad=False)
-        fl.step_tensor.fill_(float(self.step_count))
+        fl.step_vec.fill_(float(self.step_count))

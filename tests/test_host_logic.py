@@ -134,6 +134,38 @@ def test_flat_state_keeps_parameters_keys_and_optimizer_format():
     fresh.optimizer.load_state_dict(sd)     # stock torch.optim.AdamW accepts the state we expose
 
 
+def test_checkpoint_saved_after_fused_steps_resumes_in_stock_adamw():
+    """The on-disk optimizer state must resume correctly in the reference (stock torch.optim.AdamW): after loading a
+    checkpoint written between fused steps, ONE optimizer.step() advances every parameter's `step` by exactly one.
+    (A `step` tensor object shared by all states survives torch.save/torch.load as one object and would be incremented
+    once per parameter.)"""
+    import io
+    from penroz.engine import FlatState
+    m = build_gpt("resume", 1, 2, 32, 16, 11)
+    params = list(m.parameters())
+    fl = FlatState(params, need_shadow=False)
+    fl.adopt_optimizer_state(m.optimizer)
+    fl.step_vec.fill_(3.0)                                   # what three fused AdamW updates leave behind
+    fl.m.normal_(); fl.v.uniform_(0.1, 1.0)
+    buf = io.BytesIO()
+    torch.save({"state": m.state_dict(), "optim_state": m.optimizer.state_dict()}, buf, pickle_protocol=5)
+    buf.seek(0)
+    data = torch.load(buf, weights_only=False)
+    steps = [st["step"] for st in data["optim_state"]["state"].values()]
+    assert len({id(t) for t in steps}) == len(steps) == len(params)
+    fresh = build_gpt("resume2", 1, 2, 32, 16, 11)
+    fresh.load_state_dict(data["state"])
+    fresh.optimizer.load_state_dict(data["optim_state"])
+    for p in fresh.parameters():
+        p.grad = torch.ones_like(p)
+    fresh.optimizer.step()
+    assert [float(st["step"]) for st in fresh.optimizer.state.values()] == [4.0] * len(params)
+    # and the fused side picks the count up again when a caller's stock optimizer stepped in between
+    for p in params:
+        m.optimizer.state[p]["step"] += 1
+    assert float(fl.step_vec.max()) == 4.0 and float(fl.step_vec.min()) == 4.0
+
+
 def _sync_worker(rank, world, port, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
                       LOCAL_RANK=str(rank))
@@ -307,4 +339,47 @@ def test_resident_model_serialises_concurrent_requests(monkeypatch):
         for i, p in enumerate(prompts):
             assert got[i] == alone[i][len(p[0]):], i
     assert len(nnm._RESIDENT) == 1
+    nnm._RESIDENT.clear()
+
+
+def test_stream_advanced_and_closed_from_different_threads(monkeypatch):
+    """Starlette drives a sync generator with one threadpool dispatch per next() (the service wraps
+    generate_tokens_stream in a StreamingResponse, main.py:427-431): the stream of a resident model is started on one
+    thread, advanced on a second and closed on a third. The run lock must be released by the closing thread, a second
+    request must wait while the stream is open (also when it runs on the owner's thread), and the model must still be
+    locked for callers that hold it after the cache dropped its entry."""
+    import threading
+    import neural_net_model as nnm
+    scratch_cwd()
+    monkeypatch.setenv("PENROZ_MODEL_CACHE", "1")
+    nnm._RESIDENT.clear()
+    build_gpt("res_s", 2, 2, 32, 32, 17).serialize()
+    model = nnm.NeuralNetworkModel.deserialize("res_s")
+    alone = model.generate_tokens([[1, 2, 3, 4]], 32, 12, temperature=0.0)[4:]
+    stream = model.generate_tokens_stream([[1, 2, 3, 4]], 32, 12, temperature=0.0)
+    got, errors = [], []
+
+    def on_thread(fn):
+        def run():
+            try:
+                fn()
+            except Exception as e:      # noqa: BLE001 - reported below
+                errors.append(repr(e))
+        t = threading.Thread(target=run)
+        t.start()
+        t.join()
+
+    on_thread(lambda: got.append(next(stream)))
+    lock = model.__dict__["_run_lock"]
+    assert lock.locked()
+    # a second request on this (any) thread cannot enter while the stream is open
+    assert not lock.acquire(blocking=False)
+    nnm._RESIDENT.clear()                                   # evicted while a caller still streams from the object
+    assert nnm._Exclusive(model).lock is lock
+    on_thread(lambda: got.extend(next(stream) for _ in range(5)))
+    on_thread(stream.close)
+    assert not errors, errors
+    assert got == alone[:6]
+    assert not lock.locked()
+    assert model.generate_tokens([[1, 2, 3, 4]], 32, 12, temperature=0.0)[4:] == alone   # and the model is usable again
     nnm._RESIDENT.clear()

@@ -28,8 +28,10 @@ def test_colsum_static_matches_colsum_twice_in_a_row():
     dev = torch.device("cuda:0")
     st = torch.cuda.current_stream().cuda_stream
     torch.manual_seed(11)
-    # second call is narrower than the first: it must not pick up partial sums the first call left behind
-    for (M, N, dtype, accumulate) in [(4099, 3072, torch.bfloat16, 1), (513, 772, torch.float32, 0)]:
+    # second call is narrower than the first: it must not pick up partial sums the first call left behind; the third
+    # sits exactly on the built-in limit (8192 columns) and accumulates
+    for (M, N, dtype, accumulate) in [(4099, 3072, torch.bfloat16, 1), (513, 772, torch.float32, 0),
+                                      (257, 8192, torch.bfloat16, 1)]:
         x = torch.randn(M, N, device=dev).to(dtype)
         start = torch.randn(N, device=dev)
         want = start.clone()
@@ -37,10 +39,18 @@ def test_colsum_static_matches_colsum_twice_in_a_row():
         L.colsum(x.data_ptr(), x.stride(0), M, N, want.data_ptr(), accumulate, _lib.dt(x), scratch.data_ptr(),
                  scratch.numel(), st)
         got = start.clone()
+        # One untimed call per case first: the first call on a device looks up the built-in array's address, and the
+        # first launch of each kernel variant makes the driver load its code (lazy module loading), which moves the
+        # driver's free-memory figure although nobody allocated. The measured call below is an ordinary later call.
+        warm = start.clone()
+        L.colsum_static(x.data_ptr(), x.stride(0), M, N, warm.data_ptr(), accumulate, _lib.dt(x), st)
+        torch.cuda.synchronize()
         before = torch.cuda.memory_allocated()
+        free_before = torch.cuda.mem_get_info()[0]              # the driver's own count: sees a raw cudaMalloc too
         L.colsum_static(x.data_ptr(), x.stride(0), M, N, got.data_ptr(), accumulate, _lib.dt(x), st)
         torch.cuda.synchronize()
-        assert torch.cuda.memory_allocated() == before          # nothing was allocated through torch either
+        assert torch.cuda.memory_allocated() == before          # nothing was allocated through torch
+        assert torch.cuda.mem_get_info()[0] == free_before      # and nothing behind torch's back either
         assert _rel_err(got, want) < 1e-5, (M, N, dtype, _rel_err(got, want))
         ref = x.float().sum(0) + (start if accumulate else 0)
         assert _rel_err(got, ref) < 1e-5
@@ -58,3 +68,18 @@ def test_colsum_static_rejects_matrices_wider_than_its_scratch():
         L.colsum_static(x.data_ptr(), x.stride(0), 8, N, out.data_ptr(), 0, _lib.F32,
                         torch.cuda.current_stream().cuda_stream)
     assert "8192" in str(err.value) and "penroz_colsum" in str(err.value)
+
+
+def test_colsum_refuses_a_leading_dimension_shorter_than_the_row():
+    from penroz import _lib
+    _lib.require_device()
+    L = _lib.lib()
+    dev = torch.device("cuda:0")
+    x = torch.zeros(8, 64, device=dev)
+    out = torch.zeros(64, device=dev)
+    scratch = torch.empty(L.colsum_scratch_bytes(8, 64), device=dev, dtype=torch.uint8)
+    st = torch.cuda.current_stream().cuda_stream
+    with pytest.raises(_lib.PenrozError, match="leading dimension"):
+        L.colsum_static(x.data_ptr(), 32, 8, 64, out.data_ptr(), 0, _lib.F32, st)
+    with pytest.raises(_lib.PenrozError, match="leading dimension"):
+        L.colsum(x.data_ptr(), 32, 8, 64, out.data_ptr(), 0, _lib.F32, scratch.data_ptr(), scratch.numel(), st)
