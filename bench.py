@@ -582,8 +582,8 @@ def run_ours(args):
     if rank == 0:
         n = len(durs)
         e2e = {"value": tokens_per_step * n / e2e_secs.item(), "unit": UNIT,
-               "h2d_bytes_per_step": accum * 2 * B * T * 8, "d2h_bytes_per_step": 4,
-               "api": "NeuralNetworkModel.train_model (uint16 shards on the host -> pinned int64 batch -> async H2D -> "
+               "h2d_bytes_per_step": accum * 2 * B * T * 4, "d2h_bytes_per_step": 4,
+               "api": "NeuralNetworkModel.train_model (uint16 shards on the host -> pinned int32 window -> async H2D -> widened on the device -> "
                       "fused step -> cost.item()); per-epoch wall clock after torch.cuda.synchronize(), as the reference "
                       "logs it; progress (incl. weight_upd_ratio) recorded every epoch; the final stats-collecting "
                       "epoch is run but not timed",

@@ -74,6 +74,11 @@ int penroz_embed_fwd(const long long* idx, const void* wte, const void* wpe, voi
 int penroz_embed_bwd(const long long* idx, const float* dx, float* dwte, float* dwpe, int B, int T, int C, int V,
                      int pos_offset, void* stream);
 
+/* int32 token ids -> int64 on the device. Replaces the host-side widening of every batch,
+ * torch.tensor(arr, dtype=torch.long).view(B, T).to(device) (neural_net_model.py:630-631): the
+ * loader's int32 window is uploaded as it is and widened here. */
+int penroz_widen_tokens(const int* src, long long* dst, long long n, void* stream);
+
 /* ---- LayerNorm (eps as given; statistics in fp32) ----
  * Replaces nn.LayerNorm forward/backward (mappers.py:31,155,162,171). beta may be NULL (bias=False).
  * Backward also folds in the residual-stream gradient (`add`, neural_net_layers.py:130-135), can emit a bf16 copy
@@ -160,6 +165,16 @@ int penroz_ce_reduce(const float* loss_rows, int M, const int* n_valid, float ou
 int penroz_adamw_flat(float* p, float* g, float* m, float* v, void* shadow_bf16, long long n, double lr, double beta1,
                       double beta2, double eps, double weight_decay, long long step, const float* grad_mult,
                       int zero_grad, void* stream);
+/* The same AdamW pass that also measures the update it applies. Replaces, for the progress entry the
+ * reference records every epoch, the clone of every 2-D weight before the step (neural_net_model.py:619-620) and
+ * std(w - w_prev) / (std(w) + 1e-8) per weight after it (:696-699): the kernel holds w_prev and w in registers anyway.
+ * n must be a multiple of 64; seg_of_group[n / 64] (device int32) gives, per 64-element group of the flat buffer, the
+ * row of seg_stats the group's tensor accumulates into, or -1; seg_stats[row][4] (device doubles, zeroed by the caller)
+ * receives sum(d), sum(d^2), sum(w), sum(w^2) with d = w - w_prev formed in fp32 as the reference forms it. */
+int penroz_adamw_flat_stats(float* p, float* g, float* m, float* v, void* shadow_bf16, long long n, double lr,
+                            double beta1, double beta2, double eps, double weight_decay, long long step,
+                            const float* grad_mult, int zero_grad, const int* seg_of_group, double* seg_stats,
+                            void* stream);
 size_t penroz_grad_norm_scratch_bytes(long long n);
 int penroz_grad_norm(const float* g, long long n, float max_norm, float* norm_out, float* mult_out, void* scratch,
                      size_t scratch_bytes, void* stream);

@@ -306,6 +306,7 @@ def main():
     d.add_argument("--time", type=int, default=1)
     d.add_argument("--out", required=True)
     a = ap.parse_args()
+    a.out = os.path.abspath(a.out)      # the commands chdir into a scratch folder before they write
     {"train": cmd_train, "profile": cmd_profile, "decode": cmd_decode}[a.cmd](a)
 
 

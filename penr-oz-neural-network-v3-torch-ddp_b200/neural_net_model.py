@@ -674,7 +674,12 @@ class NeuralNetworkModel(nn.Module):
             t_begin = time.time()
             slow = last_saved is not None and (t_begin - last_saved >= 10)
             want_stats = master and (epoch + 1 == epochs or slow)
-            before = [None if w is None else w.clone().detach() for w in self._weights] if master else []
+            records = master and epoch % max(1, epochs // 100) == 0      # at most ~100 progress points
+            stepper.measure_update = records
+            stepper.more_epochs = epoch + 1 < epochs
+            # the fused AdamW pass measures its own update; only the torch stepper needs the reference's weight clones
+            before = ([None if w is None else w.clone().detach() for w in self._weights]
+                      if master and not stepper.measures_update else [])
             try:
                 cost, pairs = stepper.run_epoch(loader, num_steps, batch_size, block_size, want_stats)
             except Exception as exc:
@@ -695,8 +700,8 @@ class NeuralNetworkModel(nn.Module):
                 secs = time.time() - t_begin
                 speed = window / secs
                 cost_value = cost.item()
-                if epoch % max(1, epochs // 100) == 0:  # at most ~100 progress points
-                    ratios = self._weight_update_ratios(before)
+                if records:
+                    ratios = stepper.update_ratios() if stepper.measures_update else self._weight_update_ratios(before)
                     self.progress.append({"dt": dt.now().isoformat(), "epoch": epoch + 1, "durationInSecs": secs,
                                           "speedPerSec": speed, "cost": cost_value, "weight_upd_ratio": ratios})
                 log.info(f"Model {self.model_id}: Training Epoch {epoch + 1}, Cost: {cost_value:.4f}, "
@@ -829,6 +834,8 @@ class _PendingGradCost(torch.autograd.Function):
 class _TorchStepper:
     """The reference's own training step (torch autograd, optional AMP/GradScaler, stock DDP) for trees and devices
     the fused engine does not cover."""
+    measures_update = False
+    measure_update = False
 
     def __init__(self, model: NeuralNetworkModel, device, amp_ctx, amp_scaler):
         self.model, self.device, self.amp_ctx, self.scaler = model, device, amp_ctx, amp_scaler
@@ -888,36 +895,58 @@ class _FusedStepper:
     """Training step on the penroz engine: hand-written forward/backward kernels, bucketed NCCL gradient exchange
     overlapped with backward, one fused AdamW pass."""
 
+    measures_update = True       # weight_upd_ratio comes out of the AdamW pass (penroz_adamw_flat_stats): no weight clones
+
     def __init__(self, model: NeuralNetworkModel, engine, device, use_amp: bool):
         self.model, self.engine, self.device, self.use_amp = model, engine, device, use_amp
+        self.measure_update = False
+        self._keep_grads = True
         self.sync_mode = os.environ.get("PENROZ_ACCUM_SYNC", "reference")
-        self._pinned = None      # two pinned (x, y) staging pairs, reused round-robin
-        self._copied = None      # CUDA events: the H2D copy out of each pair has finished
+        self._pinned = None      # two pinned int32 [2,B,T] staging buffers, reused round-robin
+        self._copied = None      # CUDA events: the H2D copy out of each buffer has finished
         self._slot = 0
+        self._ahead = None       # a window staged ahead of time by prefetch()
+        self.more_epochs = False
 
-    def _upload(self, arrays, batch_size, block_size):
-        """Loader window (int32 numpy) -> int64 device tensors through pinned host memory, copy enqueued
-        asynchronously on the compute stream (the reference does a synchronous pageable copy per tensor,
-        neural_net_model.py:630-631)."""
-        if self._pinned is None:
-            self._pinned = [[torch.empty((batch_size, block_size), dtype=torch.long).pin_memory() for _ in range(2)]
-                            for _ in range(2)]
+    def _stage(self, arrays, batch_size, block_size):
+        """Loader window (two int32 numpy arrays) -> one pinned int32 [2,B,T] staging buffer; returns its slot. Host
+        work only: it can run while the GPU is still busy with the previous step."""
+        shape = (2, batch_size, block_size)
+        if self._pinned is None or self._pinned[0].shape != shape:
+            self._pinned = [torch.empty(shape, dtype=torch.int32).pin_memory() for _ in range(2)]
             self._copied = [None, None]
+            self._dev32 = torch.empty(shape, dtype=torch.int32, device=self.device)
+            self._dev64 = torch.empty(shape, dtype=torch.long, device=self.device)
         slot = self._slot
         self._slot ^= 1
         if self._copied[slot] is not None:
-            self._copied[slot].synchronize()      # the previous copy out of this pair is done: safe to overwrite
-        out = []
-        for host, arr in zip(self._pinned[slot], arrays):
-            if host.shape != (batch_size, block_size):
-                self._pinned = None
-                return self._upload(arrays, batch_size, block_size)
-            host.view(-1).copy_(torch.from_numpy(arr))     # int32 -> int64 widening on the host, 256 KB
-            out.append(host.to(self.device, non_blocking=True))
+            self._copied[slot].synchronize()      # the previous copy out of this buffer is done: safe to overwrite
+        host = self._pinned[slot]
+        for i, arr in enumerate(arrays):
+            host[i].view(-1).copy_(torch.from_numpy(arr))          # int32 -> int32 (no widening on the host)
+        return slot
+
+    def _upload(self, arrays, batch_size, block_size, slot=None):
+        """int32 window through pinned memory, asynchronous H2D on the compute stream, widened to the int64 ids the
+        kernels index with ON the device (penroz_widen_tokens). The reference widens on the host and does a
+        synchronous pageable copy per tensor (neural_net_model.py:630-631)."""
+        from penroz import ops
+        if slot is None:
+            slot = self._stage(arrays, batch_size, block_size)
+        self._dev32.copy_(self._pinned[slot], non_blocking=True)
         ev = torch.cuda.Event()
         ev.record()
         self._copied[slot] = ev
-        return out
+        ops.widen_tokens(self._dev32, self._dev64)
+        return self._dev64[0], self._dev64[1]
+
+    def prefetch(self, loader, batch_size, block_size):
+        """Read and stage the NEXT epoch's first window now -- after this epoch's kernels are enqueued, before the host
+        blocks on them -- so the GPU does not wait for the loader and the pinned copy after the epoch's synchronize."""
+        try:
+            self._ahead = ("ok", self._stage(loader.next_batch(), batch_size, block_size))
+        except Exception as exc:      # surfaces where the window would have been read
+            self._ahead = ("error", exc)
 
     def begin(self):
         from penroz._lib import PenrozError
@@ -958,10 +987,17 @@ class _FusedStepper:
     def run_epoch(self, loader, num_steps, batch_size, block_size, want_stats):
         eng = self.engine
         eng.zero_grad()
-        cost = torch.tensor(0.0).to(self.device)
+        self._keep_grads = bool(want_stats)
+        cost = torch.empty((), device=self.device, dtype=torch.float32)   # written by the first micro-step's loss reduction
         pairs = []
         for step in range(num_steps):
-            x, y = self._upload(loader.next_batch(), batch_size, block_size)
+            ahead, self._ahead = self._ahead, None
+            if ahead is not None and ahead[0] == "error":
+                raise ahead[1]
+            if ahead is not None:
+                x, y = self._upload(None, batch_size, block_size, slot=ahead[1])
+            else:
+                x, y = self._upload(loader.next_batch(), batch_size, block_size)
             keep = want_stats and step == 0
             eng.keep_for_stats = {} if keep else None
             # which micro-step carries the gradient exchange: the reference arms DDP one step late, so with
@@ -970,13 +1006,14 @@ class _FusedStepper:
                 (step == 0) if (self.sync_mode == "reference") else (step == num_steps - 1))
             if sync_here and self.sync_mode == "reference" and num_steps > 1:
                 pass  # later micro-steps add un-synced local gradients on top, exactly as the reference does
-            step_cost = eng.train_micro_step(x, y, 1.0 / num_steps, sync_grads=sync_here, keep_stats=keep)
+            eng.train_micro_step(x, y, 1.0 / num_steps, sync_grads=sync_here, keep_stats=keep, cost_out=cost,
+                                 cost_first=(step == 0))
             if sync_here and step != num_steps - 1:
                 eng.grad_sync.wait_all()   # later micro-steps accumulate into the reduced buffer
-            cost += step_cost / num_steps
             if keep:
                 pairs = self._stat_pairs(eng.keep_for_stats)
                 eng.keep_for_stats = None
+        self._next = (loader, batch_size, block_size)
         return cost, pairs
 
     @staticmethod
@@ -989,4 +1026,10 @@ class _FusedStepper:
         return pairs
 
     def apply_update(self, pairs):
-        self.engine.optimizer_step()
+        # on a statistics epoch the per-weight gradient summaries are read after the step: keep the gradients then
+        self.engine.optimizer_step(track_update=self.measure_update, clear_grads=not self._keep_grads)
+        if self.more_epochs:
+            self.prefetch(*self._next)
+
+    def update_ratios(self):
+        return self.engine.update_ratios()

@@ -175,11 +175,23 @@ __global__ void ce_reduce_kernel(const float* __restrict__ loss_rows, int M, con
 
 // ------------------------------------------------------------------ AdamW over flat fp32 buffers
 // Same operation order as torch's _single_tensor_adamw (param decay, lerp, addcmul, sqrt/bias-corr, addcdiv).
+// Written with explicit rounding intrinsics so that every kernel using it produces the same bits (the compiler may
+// contract a*b+c differently from one kernel to the next).
+struct AdamwCoef { float lr_wd_keep, one_minus_beta1, beta2, one_minus_beta2, eps, step_size_neg, bc2_sqrt; };
+__device__ __forceinline__ void adamw_update(float& p, float g, float& m, float& v, const AdamwCoef& c) {
+    const float pk = __fmul_rn(p, c.lr_wd_keep);                                   // param.mul_(1 - lr * wd)
+    m = __fmaf_rn(__fsub_rn(g, m), c.one_minus_beta1, m);                              // exp_avg.lerp_(grad, 1 - beta1)
+    v = __fmaf_rn(__fmul_rn(c.one_minus_beta2, g), g, __fmul_rn(v, c.beta2));          // .mul_(beta2).addcmul_(g, g, 1 - beta2)
+    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), c.bc2_sqrt), c.eps);   // sqrt / bias_correction2_sqrt + eps
+    p = __fmaf_rn(c.step_size_neg, __fdiv_rn(m, denom), pk);                       // param.addcdiv_(m, denom, -step_size)
+}
+
 __global__ void adamw_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                                   float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, size_t n, float lr_wd_keep,
-                                  float beta1, float beta2, float eps, float step_size_neg, float bc2_sqrt,
+                                  float omb1, float beta2, float omb2, float eps, float step_size_neg, float bc2_sqrt,
                                   const float* __restrict__ grad_mult, int zero_grad) {
     const float gm = grad_mult ? *grad_mult : 1.f;
+    const AdamwCoef coef{lr_wd_keep, omb1, beta2, omb2, eps, step_size_neg, bc2_sqrt};
     size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
     for (; i < n; i += stride) {
@@ -189,16 +201,8 @@ __global__ void adamw_flat_kernel(float* __restrict__ p, float* __restrict__ g, 
             float4 mv = *reinterpret_cast<float4*>(m + i);
             float4 vv = *reinterpret_cast<float4*>(v + i);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                float gk = (&gv.x)[k] * gm;
-                float pk = (&pv.x)[k] * lr_wd_keep;
-                float mk = (&mv.x)[k];
-                mk = mk + (gk - mk) * (1.f - beta1);
-                float vk = (&vv.x)[k] * beta2 + ((1.f - beta2) * gk) * gk;
-                const float denom = sqrtf(vk) / bc2_sqrt + eps;
-                pk = pk + step_size_neg * (mk / denom);
-                (&pv.x)[k] = pk; (&mv.x)[k] = mk; (&vv.x)[k] = vk;
-            }
+            for (int k = 0; k < 4; ++k)
+                adamw_update((&pv.x)[k], __fmul_rn((&gv.x)[k], gm), (&mv.x)[k], (&vv.x)[k], coef);
             *reinterpret_cast<float4*>(p + i) = pv;
             *reinterpret_cast<float4*>(m + i) = mv;
             *reinterpret_cast<float4*>(v + i) = vv;
@@ -211,19 +215,87 @@ __global__ void adamw_flat_kernel(float* __restrict__ p, float* __restrict__ g, 
             }
         } else {
             for (size_t k = i; k < n; ++k) {
-                float gk = g[k] * gm;
-                float pk = p[k] * lr_wd_keep;
-                float mk = m[k];
-                mk = mk + (gk - mk) * (1.f - beta1);
-                float vk = v[k] * beta2 + ((1.f - beta2) * gk) * gk;
-                const float denom = sqrtf(vk) / bc2_sqrt + eps;
-                pk = pk + step_size_neg * (mk / denom);
+                float pk = p[k], mk = m[k], vk = v[k];
+                adamw_update(pk, __fmul_rn(g[k], gm), mk, vk, coef);
                 p[k] = pk; m[k] = mk; v[k] = vk;
                 if (zero_grad) g[k] = 0.f;
                 if (shadow) shadow[k] = __float2bfloat16_rn(pk);
             }
         }
     }
+}
+
+// The same update, additionally folding what the reference's progress entry needs per 2-D weight -- std(w_new - w_old)
+// and std(w_new) (neural_net_model.py:619-620,696-699: a clone of every weight before the step and ~3 reductions per
+// weight after it) -- into the pass that already holds w_old and w_new in registers. The flat buffer is cut into
+// 64-element groups (every parameter starts on a group boundary); seg_of_group[group] names the tracked tensor the
+// group belongs to (-1: not tracked). A CTA sweeps a CONTIGUOUS range of the buffer, a half-warp owns one group per
+// sweep step and keeps fp64 running sums {sum d, sum d^2, sum w, sum w^2} for its current tensor; they are flushed with
+// four fp64 atomics when the tensor changes and at the end (a few thousand atomics per step in total).
+__global__ void __launch_bounds__(256)
+adamw_flat_stats_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                        __nv_bfloat16* __restrict__ shadow, size_t n, float lr_wd_keep, float omb1, float beta2,
+                        float omb2, float eps, float step_size_neg, float bc2_sqrt, const float* __restrict__ grad_mult,
+                        int zero_grad, const int* __restrict__ seg_of_group, double* __restrict__ seg_stats) {
+    const float gm = grad_mult ? *grad_mult : 1.f;
+    const AdamwCoef coef{lr_wd_keep, omb1, beta2, omb2, eps, step_size_neg, bc2_sqrt};
+    constexpr size_t TILE = 256 * 4;                       // elements per sweep step of a CTA
+    const size_t tiles = (n + TILE - 1) / TILE;
+    const size_t t0 = tiles * blockIdx.x / gridDim.x, t1 = tiles * (blockIdx.x + 1) / gridDim.x;
+    int cur = -1;
+    double sd = 0.0, sdd = 0.0, sw = 0.0, sww = 0.0;
+    const unsigned lane = threadIdx.x & 31;
+    auto flush = [&](bool mine) {                          // called by whole warps; `mine`: uniform per half-warp
+        double a = sd, b = sdd, c = sw, d = sww;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+            c += __shfl_xor_sync(0xffffffffu, c, o);
+            d += __shfl_xor_sync(0xffffffffu, d, o);
+        }
+        if (mine) {
+            if ((lane & 15) == 0 && cur >= 0) {
+                double* out = seg_stats + (size_t)cur * 4;
+                atomicAdd(out + 0, a); atomicAdd(out + 1, b); atomicAdd(out + 2, c); atomicAdd(out + 3, d);
+            }
+            sd = sdd = sw = sww = 0.0;
+        }
+    };
+    for (size_t t = t0; t < t1; ++t) {
+        const size_t i = t * TILE + (size_t)threadIdx.x * 4;
+        const bool live = i < n;                           // n is a multiple of 64: a float4 is all in or all out
+        const int seg = live ? seg_of_group[i >> 6] : cur;
+        const bool changed = seg != cur;
+        if (__any_sync(0xffffffffu, changed)) {
+            flush(changed);
+            if (changed) cur = seg;
+        }
+        if (!live) continue;
+        float4 pv = *reinterpret_cast<float4*>(p + i);
+        float4 gv = *reinterpret_cast<float4*>(g + i);
+        float4 mv = *reinterpret_cast<float4*>(m + i);
+        float4 vv = *reinterpret_cast<float4*>(v + i);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float p_old = (&pv.x)[k];
+            adamw_update((&pv.x)[k], __fmul_rn((&gv.x)[k], gm), (&mv.x)[k], (&vv.x)[k], coef);
+            const float pk = (&pv.x)[k];
+            const double dk = (double)__fsub_rn(pk, p_old), wk = (double)pk;   // w - w_prev as the reference forms it: in fp32
+            sd += dk; sdd = fma(dk, dk, sdd); sw += wk; sww = fma(wk, wk, sww);
+        }
+        *reinterpret_cast<float4*>(p + i) = pv;
+        *reinterpret_cast<float4*>(m + i) = mv;
+        *reinterpret_cast<float4*>(v + i) = vv;
+        if (zero_grad) *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (shadow) {
+            uint2 w;
+            w.x = pack_bf16x2(pv.x, pv.y);
+            w.y = pack_bf16x2(pv.z, pv.w);
+            *reinterpret_cast<uint2*>(shadow + i) = w;
+        }
+    }
+    flush(true);
 }
 
 // sum of squares -> per-block partials (scratch) -> norm, clip multiplier
@@ -327,10 +399,32 @@ extern "C" int penroz_adamw_flat(float* p, float* g, float* m, float* v, void* s
     const double step_size = lr / bc1;
     const double bc2_sqrt = sqrt(bc2);
     adamw_flat_kernel<<<flat_grid((size_t)n), 256, 0, (cudaStream_t)stream>>>(
-        p, g, m, v, (__nv_bfloat16*)shadow_bf16, (size_t)n, (float)(1.0 - lr * weight_decay), (float)beta1, (float)beta2,
-        (float)eps, (float)(-step_size), (float)bc2_sqrt, grad_mult, zero_grad);
+        p, g, m, v, (__nv_bfloat16*)shadow_bf16, (size_t)n, (float)(1.0 - lr * weight_decay), (float)(1.0 - beta1), (float)beta2,
+        (float)(1.0 - beta2), (float)eps, (float)(-step_size), (float)bc2_sqrt, grad_mult, zero_grad);
     count_launch();
     return check_launch("adamw_flat");
+}
+
+extern "C" int penroz_adamw_flat_stats(float* p, float* g, float* m, float* v, void* shadow_bf16, long long n, double lr,
+                                       double beta1, double beta2, double eps, double weight_decay, long long step,
+                                       const float* grad_mult, int zero_grad, const int* seg_of_group,
+                                       double* seg_stats, void* stream) {
+    PENROZ_REQUIRE(n > 0 && p && g && m && v && seg_of_group && seg_stats, "adamw_flat_stats: bad arguments");
+    PENROZ_REQUIRE(n % 64 == 0, "adamw_flat_stats: n=%lld must be a multiple of the 64-element group", n);
+    PENROZ_REQUIRE(step >= 1, "adamw_flat_stats: step must be >= 1");
+    PENROZ_REQUIRE(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0, "adamw_flat_stats: buffers must be 16-byte aligned");
+    const double bc1 = 1.0 - pow(beta1, (double)step);
+    const double bc2 = 1.0 - pow(beta2, (double)step);
+    const double step_size = lr / bc1;
+    const double bc2_sqrt = sqrt(bc2);
+    size_t tiles = ((size_t)n + 1023) / 1024;
+    size_t grid = (size_t)num_sms() * 8;
+    if (grid > tiles) grid = tiles;
+    adamw_flat_stats_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>(
+        p, g, m, v, (__nv_bfloat16*)shadow_bf16, (size_t)n, (float)(1.0 - lr * weight_decay), (float)(1.0 - beta1), (float)beta2,
+        (float)(1.0 - beta2), (float)eps, (float)(-step_size), (float)bc2_sqrt, grad_mult, zero_grad, seg_of_group, seg_stats);
+    count_launch();
+    return check_launch("adamw_flat_stats");
 }
 
 extern "C" size_t penroz_grad_norm_scratch_bytes(long long n) { return (size_t)flat_grid((size_t)n) * sizeof(float); }

@@ -534,6 +534,36 @@ static inline int grid_for(size_t n_vec4, int threads) {
     return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
+// int32 token ids (what the shard loader yields, loaders.py:62-63) -> the int64 ids the embedding and cross-entropy
+// kernels index with. The reference widens on the host (torch.tensor(arr, dtype=torch.long), neural_net_model.py:630);
+// here the int32 window is what crosses PCIe (half the bytes) and the GPU widens it.
+namespace penroz {
+__global__ void widen_tokens_kernel(const int* __restrict__ src, long long* __restrict__ dst, size_t n) {
+    size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+    for (; i < n; i += stride) {
+        if (i + 3 < n) {
+            const int4 v = *reinterpret_cast<const int4*>(src + i);
+            longlong2 a, b;
+            a.x = v.x; a.y = v.y; b.x = v.z; b.y = v.w;
+            *reinterpret_cast<longlong2*>(dst + i) = a;
+            *reinterpret_cast<longlong2*>(dst + i + 2) = b;
+        } else {
+            for (size_t k = i; k < n; ++k) dst[k] = src[k];
+        }
+    }
+}
+}  // namespace penroz
+
+extern "C" int penroz_widen_tokens(const int* src, long long* dst, long long n, void* stream) {
+    PENROZ_REQUIRE(src && dst && n > 0, "widen_tokens: bad arguments");
+    PENROZ_REQUIRE(((uintptr_t)src | (uintptr_t)dst) % 16 == 0, "widen_tokens: buffers must be 16-byte aligned");
+    const int grid = grid_for((size_t)(n + 3) / 4, 256);
+    penroz::widen_tokens_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, (size_t)n);
+    count_launch();
+    return check_launch("widen_tokens");
+}
+
 extern "C" int penroz_embed_fwd(const long long* idx, const void* wte, const void* wpe, void* out, int B, int T,
                                 int C, int V, int pos_offset, int w_dtype, int out_dtype, int* err_flag,
                                 void* stream) {

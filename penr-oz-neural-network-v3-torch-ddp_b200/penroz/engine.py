@@ -58,6 +58,13 @@ class FlatState:
                 p.data = view
                 p.grad = self.g[off:off + p.numel()].view(p.shape)
         self._index = {id(p): i for i, p in enumerate(params)}
+        # which tracked tensor (= parameter index, 2-D weights only) each 64-element group of the flat buffer belongs to
+        seg = torch.full((total // _ALIGN,), -1, dtype=torch.int32)
+        for i, (p, off) in enumerate(zip(params, self.offsets)):
+            if p.ndim == 2:
+                seg[off // _ALIGN:(off + _round_up(p.numel(), _ALIGN)) // _ALIGN] = i
+        self.seg_of_group = seg.to(dev)
+        self.update_stats = torch.zeros((len(params), 4), device=dev, dtype=torch.float64)
         if need_shadow:
             self.refresh_shadow()
 
@@ -352,7 +359,10 @@ class Gpt2Engine:
         self.flat.rebind_grads()
 
     def zero_grad(self):
-        self.flat.g.zero_()
+        # the previous fused AdamW pass may already have cleared the gradients it consumed (one 4-byte store per element
+        # it was touching anyway, instead of a separate 4 P-byte fill)
+        if not getattr(self, "_grads_clean", False):
+            self.flat.g.zero_()
         self.flat.rebind_grads()
 
     def _buf(self, name, shape, dtype):
@@ -367,10 +377,13 @@ class Gpt2Engine:
         self._ws.clear()
 
     # ------------------------------------------------------------------ one micro-step: forward + backward
-    def train_micro_step(self, idx, targets, grad_scale: float, sync_grads: bool = False, keep_stats: bool = False):
+    def train_micro_step(self, idx, targets, grad_scale: float, sync_grads: bool = False, keep_stats: bool = False,
+                         cost_out=None, cost_first: bool = True):
         """Forward + backward of one (B,T) micro-batch; gradients are ACCUMULATED (+=) into the flat buffer scaled by
         grad_scale (= 1/num_steps, neural_net_model.py:636). Returns the micro-batch mean loss (device scalar).
-        sync_grads: launch the bucketed all-reduce of each bucket as soon as its gradients are final."""
+        sync_grads: launch the bucketed all-reduce of each bucket as soon as its gradients are final.
+        cost_out: 0-dim fp32 device tensor receiving the epoch cost `cost += step_cost / num_steps` (:636-638) from the
+        loss reduction itself (set on the first micro-step, added to on later ones)."""
         pl, fl = self.plan, self.flat
         amp = self.mode == "amp"
         act = torch.bfloat16 if amp else torch.float32
@@ -382,6 +395,7 @@ class Gpt2Engine:
         idx = idx.contiguous()
         targets = targets.reshape(-1).contiguous()
         buf = self._buf
+        self._grads_clean = False
         gs = self.grad_sync if sync_grads else None
         self._err_flag.zero_()
 
@@ -450,6 +464,8 @@ class Gpt2Engine:
             if pl.head.bias is not None:
                 ops.colsum(dl, fl.grad(pl.head.bias), accumulate=True, scratch=self._scratch(M, self._widest()))
         ops.ce_reduce(loss_rows, n_valid, loss)
+        if cost_out is not None:
+            ops.ce_reduce(loss_rows, n_valid, cost_out, out_scale=grad_scale, accumulate=not cost_first)
 
         # ---------------- backward through the blocks
         scratch = self._scratch(M, self._widest())
@@ -572,6 +588,7 @@ class Gpt2Engine:
     def backward_pending(self, grad_out):
         fl = self.flat
         dropped = [p for p in self.parameters if p.grad is None]
+        self._grads_clean = False
         if len(dropped) == len(self.parameters):
             fl.g.zero_()
         else:
@@ -592,9 +609,11 @@ class Gpt2Engine:
         return self._buf("scratch", (int(need),), torch.uint8)
 
     # ------------------------------------------------------------------ optimizer
-    def optimizer_step(self):
+    def optimizer_step(self, track_update: bool = False, clear_grads: bool = False):
         """One AdamW update over the flat buffers with the hyper-parameters of the (stock) torch optimizer's single
-        param group; also refreshes the bf16 shadow weights in the same pass."""
+        param group; also refreshes the bf16 shadow weights in the same pass. track_update: the pass also measures the
+        update per 2-D weight (update_ratios() reads it). clear_grads: the pass zeroes the gradients it consumed (the
+        caller does not look at .grad afterwards), so the next zero_grad() costs nothing."""
         fl = self.flat
         gs = self.grad_sync
         # With every bucket still in flight (the usual one-micro-step epoch) the update runs bucket by bucket in
@@ -620,8 +639,29 @@ class Gpt2Engine:
             mult = self._buf("gmult", (1,), torch.float32)
             ops.grad_norm(fl.g, self.clip_grad_norm, norm, mult)
         shadow = fl.shadow if self.mode == "amp" else None
+        if track_update:
+            fl.update_stats.zero_()
         for lo, hi in (ranges if ranges is not None else [(0, fl.p.numel())]):
             ops.adamw_flat(fl.p[lo:hi], fl.g[lo:hi], fl.m[lo:hi], fl.v[lo:hi], None if shadow is None else shadow[lo:hi],
                            lr=grp["lr"], betas=grp["betas"], eps=grp["eps"], weight_decay=grp["weight_decay"],
-                           step=self.step_count, grad_mult=mult, zero_grad=False)
+                           step=self.step_count, grad_mult=mult, zero_grad=clear_grads,
+                           seg_of_group=fl.seg_of_group[lo // _ALIGN:hi // _ALIGN] if track_update else None,
+                           seg_stats=fl.update_stats if track_update else None)
+        self._grads_clean = bool(clear_grads)
         fl.step_vec.fill_(float(self.step_count))
+
+    def update_ratios(self) -> list:
+        """std(w - w_prev) / (std(w) + 1e-8) per parameter for the last optimizer_step(track_update=True), None for
+        parameters that are not 2-D weights: the reference's `weight_upd_ratio` (neural_net_model.py:696-699; torch's
+        std is the unbiased one) from the sums the AdamW pass accumulated -- one small device->host read."""
+        vals = self.flat.update_stats.tolist()
+        out = []
+        for p, (sd, sdd, sw, sww) in zip(self.parameters, vals):
+            n = p.numel()
+            if p.ndim != 2 or n < 2:
+                out.append(None)
+                continue
+            var_d = max(0.0, (sdd - sd * sd / n) / (n - 1))
+            var_w = max(0.0, (sww - sw * sw / n) / (n - 1))
+            out.append(var_d ** 0.5 / (var_w ** 0.5 + 1e-8))
+        return out

@@ -63,6 +63,12 @@ def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=Non
     return (out, out2) if epilogue == EPI_GELU else out
 
 
+def widen_tokens(src_i32, dst_i64):
+    """int32 token ids -> int64, on the device (dst may be any int64 tensor with as many elements)."""
+    lib().widen_tokens(ptr(src_i32), ptr(dst_i64), src_i32.numel(), stream())
+    return dst_i64
+
+
 def embed_fwd(idx, wte, wpe, pos_offset=0, out_dtype=None, err_flag=None, out=None):
     idx = idx.contiguous()
     B, T = idx.shape
@@ -215,7 +221,15 @@ def ce_reduce(loss_rows, n_valid, loss_out, out_scale=1.0, accumulate=False):
                     stream())
 
 
-def adamw_flat(p, g, m, v, shadow, *, lr, betas, eps, weight_decay, step, grad_mult=None, zero_grad=False):
+def adamw_flat(p, g, m, v, shadow, *, lr, betas, eps, weight_decay, step, grad_mult=None, zero_grad=False,
+               seg_of_group=None, seg_stats=None):
+    """One AdamW pass over flat buffers. With seg_of_group / seg_stats (see penroz_adamw_flat_stats) the pass also
+    accumulates sum(d), sum(d^2), sum(w), sum(w^2) of the update d = w - w_prev per tracked tensor."""
+    if seg_of_group is not None:
+        lib().adamw_flat_stats(ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), p.numel(), float(lr), float(betas[0]),
+                               float(betas[1]), float(eps), float(weight_decay), int(step), ptr(grad_mult),
+                               int(zero_grad), ptr(seg_of_group), ptr(seg_stats), stream())
+        return
     lib().adamw_flat(ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), p.numel(), float(lr), float(betas[0]),
                      float(betas[1]), float(eps), float(weight_decay), int(step), ptr(grad_mult), int(zero_grad),
                      stream())

@@ -5,6 +5,8 @@ bf16-rounded inputs; the bound is a few bf16 ulps of the output scale (2^-8 rela
 """
 import math
 
+import numpy as np
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -349,6 +351,56 @@ def test_adamw_and_grad_norm(dev):
     ops.grad_norm(g, 1.0, norm, mult)
     assert abs(norm.item() - g.double().norm().item()) < 1e-3 * g.norm().item()
     assert abs(mult.item() - min(1.0, 1.0 / (g.norm().item() + 1e-6))) < 1e-5
+
+
+def test_adamw_pass_measures_its_own_update(dev):
+    """penroz_adamw_flat_stats: the same parameters / moments / shadow as penroz_adamw_flat bit for bit, plus, per tracked
+    tensor, the sums behind the reference's weight_upd_ratio = std(w - w_prev) / (std(w) + 1e-8)
+    (neural_net_model.py:696-699), checked against torch on cloned weights -- also when the pass is split into
+    ranges (the bucket-wise update under DDP) and when a tracked tensor is smaller than a sweep tile."""
+    from penroz import ops
+    torch.manual_seed(9)
+    sizes = [(65, 128), (128,), (384, 128), (384,), (3, 64), (50257, 16), (7,)]      # 2-D ones are tracked
+    offs, total = [], 0
+    for shp in sizes:
+        offs.append(total)
+        total += (int(np.prod(shp)) + 63) // 64 * 64
+    p = torch.zeros(total, device=dev); g = torch.zeros(total, device=dev)
+    for shp, off in zip(sizes, offs):
+        n = int(np.prod(shp))
+        p[off:off + n] = torch.randn(n, device=dev) * 0.02
+        g[off:off + n] = torch.randn(n, device=dev) * 1e-3
+    seg = torch.full((total // 64,), -1, dtype=torch.int32)
+    for i, (shp, off) in enumerate(zip(sizes, offs)):
+        if len(shp) == 2:
+            seg[off // 64:(off + (int(np.prod(shp)) + 63) // 64 * 64) // 64] = i
+    seg = seg.to(dev)
+    kw = dict(lr=6e-4, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.01)
+    for split in (None, [0, offs[2], offs[5], total]):
+        p1, p2 = p.clone(), p.clone()
+        m1, v1, m2, v2 = (torch.zeros(total, device=dev) for _ in range(4))
+        s1 = torch.empty(total, device=dev, dtype=torch.bfloat16); s2 = torch.empty_like(s1)
+        g1, g2 = g.clone(), g.clone()
+        stats = torch.zeros(len(sizes), 4, device=dev, dtype=torch.float64)
+        for step in (1, 2):
+            before = p2.clone()
+            ops.adamw_flat(p1, g1, m1, v1, s1, step=step, **kw)
+            stats.zero_()
+            for lo, hi in (zip(split[:-1], split[1:]) if split else [(0, total)]):
+                ops.adamw_flat(p2[lo:hi], g2[lo:hi], m2[lo:hi], v2[lo:hi], s2[lo:hi], step=step, zero_grad=False,
+                               seg_of_group=seg[lo // 64:hi // 64], seg_stats=stats, **kw)
+            assert torch.equal(p1, p2) and torch.equal(m1, m2) and torch.equal(v1, v2) and torch.equal(s1, s2)
+            vals = stats.tolist()
+            for i, (shp, off) in enumerate(zip(sizes, offs)):
+                n = int(np.prod(shp))
+                if len(shp) != 2:
+                    assert vals[i] == [0.0] * 4
+                    continue
+                w, pw = p2[off:off + n], before[off:off + n]
+                want = ((w - pw).std() / (w.std() + 1e-8)).item()
+                sd, sdd, sw, sww = vals[i]
+                got = (max(0.0, (sdd - sd * sd / n) / (n - 1)) ** 0.5) / (max(0.0, (sww - sw * sw / n) / (n - 1)) ** 0.5 + 1e-8)
+                assert abs(got - want) <= 1e-4 * abs(want), (i, got, want)
 
 
 # ------------------------------------------------------------------ decode kernels
