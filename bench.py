@@ -324,6 +324,13 @@ def decode_bench(torch, nnm, cfg, full_grid=False):
                 out[f"{tag}_b{B}_topk50"] = decode_case(torch, model, cfg, B, 960, 64, es, greedy=False)
                 if tag == "bf16":   # crosses block_size: clear + re-prefill of the cropped context on every later token
                     out[f"{tag}_b{B}_cross_block"] = decode_case(torch, model, cfg, B, 1016, 16, es)
+                if tag == "f32":    # TURBO_QUANT_KV_CACHE=1: int8 codes + per-token scales, de-quantised inside attention
+                    import kv_cache
+                    kv_cache.TURBO_QUANT_ENABLED = True
+                    try:
+                        out[f"{tag}_b{B}_int8kv"] = decode_case(torch, model, cfg, B, 960, 64, es)
+                    finally:
+                        kv_cache.TURBO_QUANT_ENABLED = False
         del model
         torch.cuda.empty_cache()
     out["workload"] = ("GPT-2 124M generate_tokens, greedy, 960-token prompt + 64 new tokens (prefill included in "
@@ -490,7 +497,9 @@ def run_ours(args):
             if sync_here and s != accum - 1:
                 eng.grad_sync.wait_all()
             loss = part / accum if loss is None else loss + part / accum
-        eng.optimizer_step()
+        # as _FusedStepper.apply_update does on an ordinary (non-statistics) epoch: rank 0 records the progress entry
+        # (weight_upd_ratio measured inside the AdamW pass), the pass clears the gradients it consumed
+        eng.optimizer_step(track_update=(rank == 0), clear_grads=True)
         return loss
 
     for i in range(args.warmup):

@@ -201,6 +201,21 @@ int penroz_kv_append(const void* qkv, void* pool, const int* block_table, int ma
 size_t penroz_attn_decode_scratch_bytes(int B, int H, int D, int t_len);
 int penroz_attn_decode(const void* qkv, const void* pool, const int* block_table, int max_pages, void* out, int B,
                        int H, int D, int t_len, int dtype, void* scratch, size_t scratch_bytes, void* stream);
+/* ---- int8 KV cache (TURBO_QUANT_KV_CACHE=1) ----
+ * Replaces TurboQuantKVCache._quantize / append / _dequantize (kv_cache.py:119-125, 137-168, 135): one scale per cached
+ * token and head (amax|x| / 127, 1 where that is 0), codes = round(x / scale) clamped to [-128, 127]. codes is an int8
+ * pool [n_pages][2][H][PAGE][D], scales a pool [n_pages][2][H][PAGE] of the model dtype, both addressed through the
+ * same block table as the exact cache. kv_append_q8 quantises the K and V columns of S new rows of qkv [B*S, 3C];
+ * writeback != 0 also overwrites those columns with codes.float() * scale (what the reference's append hands to the
+ * prompt's own attention). recip_scale != 0 computes the scale as amax * (1/127) in fp32 -- what ATen does for a CUDA
+ * tensor divided by a Python scalar, so codes and scales equal the torch class's bit for bit on the GPU; 0 is the true
+ * division of CPU tensors. attn_decode_q8 is penroz_attn_decode reading that cache, de-quantising inside the kernel. */
+int penroz_kv_append_q8(void* qkv, void* codes, void* scales, const int* block_table, int max_pages, int B, int S,
+                        int H, int D, int t0, int dtype, int writeback, int recip_scale, void* stream);
+size_t penroz_attn_decode_q8_scratch_bytes(int B, int H, int D);
+int penroz_attn_decode_q8(const void* qkv, const void* codes, const void* scales, const int* block_table,
+                          int max_pages, void* out, int B, int H, int D, int t_len, int dtype, void* scratch,
+                          size_t scratch_bytes, void* stream);
 /* few-row Linear (M small): epilogue 0 store, 1 GELU, 2 residual add; out_f32 (optional) receives an fp32 copy */
 int penroz_skinny_linear(const void* x, long long ldx, const void* W, long long ldw, const void* bias, void* out,
                          long long ldo, const void* aux, long long ldaux, float* out_f32, long long ldo32, int M,
@@ -221,6 +236,8 @@ typedef struct penroz_gpt2_layer_t {
     void* kv_pool;
     float ln1_eps, ln2_eps;
     int gelu_tanh, ffn;
+    void* kv_scales;        /* int8 cache (kv_quant != 0): kv_pool holds int8 codes, this the per-token scales; else NULL */
+    int kv_quant, kv_recip; /* kv_recip: see penroz_kv_append_q8's recip_scale */
 } penroz_gpt2_layer_t;
 size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F, int t_len_max);
 /* The prompt pass that starts a generation (neural_net_model.py:387-390 with an empty cache): all S positions through

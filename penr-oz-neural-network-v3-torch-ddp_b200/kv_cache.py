@@ -118,13 +118,15 @@ class KVCache:
                  f"compression_ratio={m.compression_ratio:.2f}, last_append={m.last_append_latency_ms:.3f}ms")
 
     # ---- paged store, used by the fused decode path -------------------------------------------------------------
+    _quantised = False       # TurboQuantKVCache: the paged store keeps int8 codes + scales
+
     def paged(self, B: int, H: int, D: int, dtype, device, capacity_hint: int = 0) -> "_PagedStore":
         if self._paged is None:
-            self._paged = _PagedStore(self._num_layers, B, H, D, dtype, device, capacity_hint)
+            self._paged = _PagedStore(self._num_layers, B, H, D, dtype, device, capacity_hint, quant=self._quantised)
         elif not self._paged.compatible(B, H, D, dtype, device):
             if self._paged.length > 0:
                 raise ValueError("paged KV cache: batch/head shape changed while tokens are cached")
-            self._paged = _PagedStore(self._num_layers, B, H, D, dtype, device, capacity_hint)
+            self._paged = _PagedStore(self._num_layers, B, H, D, dtype, device, capacity_hint, quant=self._quantised)
         return self._paged
 
     # engine-facing façade (valid after paged(...) was called)
@@ -135,6 +137,9 @@ class KVCache:
 
     def pool(self, layer_idx: int) -> Tensor:
         return self._paged.pools[layer_idx]
+
+    def scale_pool(self, layer_idx: int):
+        return self._paged.scale_pools[layer_idx] if self._paged.quant else None
 
     @property
     def block_table(self) -> Tensor:
@@ -158,14 +163,17 @@ class KVCache:
 
 
 class _PagedStore:
-    def __init__(self, num_layers, B, H, D, dtype, device, capacity_hint):
+    def __init__(self, num_layers, B, H, D, dtype, device, capacity_hint, quant=False):
         from penroz import _lib
         self.PAGE = _lib.lib().kv_page_size()
         self.L, self.B, self.H, self.D, self.dtype, self.device = num_layers, B, H, D, dtype, device
+        self.quant = quant           # int8 codes + one scale per cached token and head (TurboQuantKVCache)
         self.max_pages = max(1, (max(capacity_hint, 1) + self.PAGE - 1) // self.PAGE)
         self.n_pages = B * self.max_pages
-        self.pools = [torch.empty(self.n_pages, 2, H, self.PAGE, D, device=device, dtype=dtype)
-                      for _ in range(num_layers)]
+        self.pools = [torch.empty(self.n_pages, 2, H, self.PAGE, D, device=device,
+                                  dtype=torch.int8 if quant else dtype) for _ in range(num_layers)]
+        self.scale_pools = ([torch.empty(self.n_pages, 2, H, self.PAGE, device=device, dtype=dtype)
+                             for _ in range(num_layers)] if quant else None)
         self.table_host = torch.full((B, self.max_pages), 0, dtype=torch.int32)
         self.table_dev = self.table_host.to(device)
         self.free = list(range(self.n_pages - 1, -1, -1))
@@ -185,8 +193,11 @@ class _PagedStore:
         new_max = max(2 * self.max_pages, need_pages_per_seq)
         add = self.B * (new_max - self.max_pages)
         for i, p in enumerate(self.pools):
-            extra = torch.empty(add, 2, self.H, self.PAGE, self.D, device=self.device, dtype=self.dtype)
+            extra = torch.empty(add, 2, self.H, self.PAGE, self.D, device=self.device, dtype=p.dtype)
             self.pools[i] = torch.cat([p, extra], dim=0)
+            if self.quant:
+                more = torch.empty(add, 2, self.H, self.PAGE, device=self.device, dtype=self.dtype)
+                self.scale_pools[i] = torch.cat([self.scale_pools[i], more], dim=0)
         self.native_layers = None      # page pools moved: the native decode step's pointer table is stale
         self.free = list(range(self.n_pages + add - 1, self.n_pages - 1, -1)) + self.free
         self.n_pages += add
@@ -215,20 +226,46 @@ class _PagedStore:
         from penroz import ops
         if layer_idx == 0:
             self._ensure(t0 + S)
-        ops.kv_append(qkv2d, self.pools[layer_idx], self.table_dev, B, S, self.H, self.D, t0)
+        if self.quant:
+            # a multi-token append is the prompt pass: its own attention reads the de-quantised K/V (kv_cache.py:165-168)
+            ops.kv_append_q8(qkv2d, self.pools[layer_idx], self.scale_pools[layer_idx], self.table_dev, B, S, self.H,
+                             self.D, t0, writeback=(S > 1))
+        else:
+            ops.kv_append(qkv2d, self.pools[layer_idx], self.table_dev, B, S, self.H, self.D, t0)
 
     def gather(self, layer_idx):
         n = (self.length + self.PAGE - 1) // self.PAGE
         idx = self.table_dev[:, :n].long()                       # [B, n]
         pages = self.pools[layer_idx][idx]                       # [B, n, 2, H, PAGE, D]
+        if self.quant:                                           # codes.float() * scale, as _dequantize returns them
+            pages = pages.float() * self.scale_pools[layer_idx][idx].unsqueeze(-1)
         kv = pages.permute(2, 0, 3, 1, 4, 5).reshape(2, self.B, self.H, n * self.PAGE, self.D)[:, :, :, :self.length]
         return kv[0], kv[1]
 
 
 class TurboQuantKVCache(KVCache):
     """KV cache that stores int8 codes with one scale per cached token (absmax / 127) and hands back de-quantised
-    float tensors (reference: kv_cache.py:101-195). Enabled by TURBO_QUANT_KV_CACHE=1. Host-side torch ops only:
-    a fused quantise-on-append kernel is a later row."""
+    float tensors (reference: kv_cache.py:101-195). Enabled by TURBO_QUANT_KV_CACHE=1. Generic callers go through
+    append()/get() (torch ops on growing slabs, the reference's arithmetic); the fused decode path keeps the codes in a
+    paged int8 pool written by penroz_kv_append_q8 and read by penroz_attn_decode_q8."""
+    _quantised = True
+
+    def account_tokens(self, n_tokens: int, bytes_per_layer: int, n_layers: int):
+        """Metrics for appends done inside the native decode step: what append() would have counted per layer."""
+        st = self._paged
+        es = bytes_per_layer // max(1, 2 * st.B * n_tokens * st.H * st.D)          # bytes per uncompressed element
+        rows = 2 * st.B * n_tokens * st.H                                            # (k|v, sequence, token, head) rows
+        m = self._metrics
+        m.num_appends += n_layers
+        m.total_entries += n_tokens * n_layers
+        m.memory_bytes += bytes_per_layer * n_layers
+        m.compressed_memory_bytes += rows * (st.D + es) * n_layers                  # int8 codes + one scale per row
+        m.compression_ratio = m.memory_bytes / m.compressed_memory_bytes if m.compressed_memory_bytes > 0 else 1.0
+
+    def write_packed(self, layer_idx: int, qkv2d: Tensor, B: int, S: int, t0: int):
+        self._paged.write(layer_idx, qkv2d, B, S, t0)
+        if layer_idx == self._num_layers - 1:
+            self.account_tokens(S, 2 * B * S * self._paged.H * self._paged.D * qkv2d.element_size(), self._num_layers)
 
     def __init__(self, num_layers: int = 0):
         super().__init__(num_layers)

@@ -505,8 +505,9 @@ class NeuralNetworkModel(nn.Module):
             for pe in positions:
                 pe.position_offset = offset
         engine = self._engine()
+        # the exact cache, or the int8 one (TURBO_QUANT_KV_CACHE=1): both have a paged store behind the fused step
         fused = (engine is not None and model_input.is_cuda and kv_cache is not None
-                 and type(kv_cache) is KVCache)
+                 and type(kv_cache) in (KVCache, TurboQuantKVCache))
         if fused:
             B = model_input.shape[0]
             pl = self._plan

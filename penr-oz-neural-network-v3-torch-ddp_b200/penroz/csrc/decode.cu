@@ -357,7 +357,14 @@ struct penroz_gpt2_layer_t {
     void* kv_pool;
     float ln1_eps, ln2_eps;
     int gelu_tanh, ffn;
+    void* kv_scales;             // int8 cache: per-token scales beside the int8 kv_pool (NULL: exact cache)
+    int kv_quant, kv_recip;
 };
+extern "C" {
+int penroz_kv_append_q8(void*, void*, void*, const int*, int, int, int, int, int, int, int, int, int, void*);
+int penroz_attn_decode_q8(const void*, const void*, const void*, const int*, int, void*, int, int, int, int, int, void*,
+                          size_t, void*);
+}
 
 namespace penroz {
 // y = epi(x W^T + b): skinny kernel for few rows, tensor-core / FP32-pipe GEMM otherwise. epi: 0 store, 1 gelu, 2 resid
@@ -419,7 +426,8 @@ extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte,
     void* hpre = carve((size_t)B * F);
     void* attn_scratch = w;
     const size_t attn_scratch_bytes = penroz_attn_decode_scratch_bytes(B, H, D, pos + 1);
-    if (decode_small_supported(B, C, H, dtype) && !getenv("PENROZ_DECODE_UNFUSED")) {
+    const bool q8 = layers[0].kv_quant != 0;      // int8 cache: one kernel per op, quantise-on-append + dequantising attention
+    if (!q8 && decode_small_supported(B, C, H, dtype) && !getenv("PENROZ_DECODE_UNFUSED")) {
         void* extra = w + ((attn_scratch_bytes + 255) / 256) * 256;
         return decode_step_small(tokens, wte, wpe, layers, n_layer, lnf_w, lnf_b, lnf_eps, head_w, head_b, block_table,
                                  max_pages, B, C, H, V, pos, dtype, xa, xb, qkv, att, g, (float*)attn_scratch, extra,
@@ -432,8 +440,13 @@ extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte,
         const penroz_gpt2_layer_t& L = layers[l];
         if ((rc = penroz_layernorm_fwd(x, L.ln1_w, L.ln1_b, ln, nullptr, nullptr, B, C, L.ln1_eps, dtype, dtype, dtype, stream))) return rc;
         if ((rc = decode_linear(ln, L.qkv_w, L.qkv_b, qkv, nullptr, B, 3 * C, C, 0, 0, dtype, nullptr, stream))) return rc;
-        if ((rc = penroz_kv_append(qkv, L.kv_pool, block_table, max_pages, B, 1, H, D, pos, dtype, stream))) return rc;
-        if ((rc = penroz_attn_decode(qkv, L.kv_pool, block_table, max_pages, att, B, H, D, pos + 1, dtype, attn_scratch, attn_scratch_bytes, stream))) return rc;
+        if (q8) {
+            if ((rc = penroz_kv_append_q8(qkv, L.kv_pool, L.kv_scales, block_table, max_pages, B, 1, H, D, pos, dtype, 0, L.kv_recip, stream))) return rc;
+            if ((rc = penroz_attn_decode_q8(qkv, L.kv_pool, L.kv_scales, block_table, max_pages, att, B, H, D, pos + 1, dtype, attn_scratch, attn_scratch_bytes, stream))) return rc;
+        } else {
+            if ((rc = penroz_kv_append(qkv, L.kv_pool, block_table, max_pages, B, 1, H, D, pos, dtype, stream))) return rc;
+            if ((rc = penroz_attn_decode(qkv, L.kv_pool, block_table, max_pages, att, B, H, D, pos + 1, dtype, attn_scratch, attn_scratch_bytes, stream))) return rc;
+        }
         if ((rc = decode_linear(att, L.proj_w, L.proj_b, xo, x, B, C, C, 2, 0, dtype, nullptr, stream))) return rc;
         if ((rc = penroz_layernorm_fwd(xo, L.ln2_w, L.ln2_b, ln, nullptr, nullptr, B, C, L.ln2_eps, dtype, dtype, dtype, stream))) return rc;
         if ((rc = decode_linear(ln, L.fc_w, L.fc_b, g, nullptr, B, L.ffn, C, 1, L.gelu_tanh, dtype, hpre, stream))) return rc;
@@ -495,7 +508,11 @@ extern "C" int penroz_gpt2_prefill(const long long* tokens, const void* wte, con
         const penroz_gpt2_layer_t& L = layers[l];
         if ((rc = penroz_layernorm_fwd(x, L.ln1_w, L.ln1_b, ln, nullptr, nullptr, M, C, L.ln1_eps, dtype, dtype, dtype, stream))) return rc;
         if ((rc = decode_linear(ln, L.qkv_w, L.qkv_b, qkv, nullptr, M, 3 * C, C, 0, 0, dtype, nullptr, stream))) return rc;
-        if ((rc = penroz_kv_append(qkv, L.kv_pool, block_table, max_pages, B, S, H, D, 0, dtype, stream))) return rc;
+        // int8 cache: the prompt's own attention already sees the de-quantised K/V (KVCache.append returns them,
+        // kv_cache.py:165-168), so the append writes codes.float() * scale back over the K and V columns of qkv
+        if (L.kv_quant) rc = penroz_kv_append_q8(qkv, L.kv_pool, L.kv_scales, block_table, max_pages, B, S, H, D, 0, dtype, 1, L.kv_recip, stream);
+        else rc = penroz_kv_append(qkv, L.kv_pool, block_table, max_pages, B, S, H, D, 0, dtype, stream);
+        if (rc) return rc;
         if (tc_attn) rc = penroz_attn_fwd_tc(qkv, att, nullptr, B, S, H, D, stream);
         else rc = penroz_attn_fwd_simt(qkv, att, nullptr, B, S, H, D, dtype, stream);
         if (rc) return rc;

@@ -496,6 +496,8 @@ struct penroz_gpt2_layer_t {   // same layout as include/penroz_b200.h
     void* kv_pool;
     float ln1_eps, ln2_eps;
     int gelu_tanh, ffn;
+    void* kv_scales;
+    int kv_quant, kv_recip;
 };
 
 namespace penroz {

@@ -171,7 +171,8 @@ class Gpt2Engine:
             _fields_ = [(n, ctypes.c_void_p) for n in ("ln1_w", "ln1_b", "qkv_w", "qkv_b", "proj_w", "proj_b", "ln2_w",
                                                         "ln2_b", "fc_w", "fc_b", "proj2_w", "proj2_b", "kv_pool")] + \
                        [("ln1_eps", ctypes.c_float), ("ln2_eps", ctypes.c_float), ("gelu_tanh", ctypes.c_int),
-                        ("ffn", ctypes.c_int)]
+                        ("ffn", ctypes.c_int), ("kv_scales", ctypes.c_void_p), ("kv_quant", ctypes.c_int),
+                        ("kv_recip", ctypes.c_int)]
 
         def ptr(p):
             return None if p is None else p.data_ptr()
@@ -188,6 +189,8 @@ class Gpt2Engine:
             L.kv_pool = store.pools[i].data_ptr()
             L.ln1_eps, L.ln2_eps = blk.ln1.eps, blk.ln2.eps
             L.gelu_tanh, L.ffn = int(blk.gelu_tanh), blk.fc.out_features
+            L.kv_scales = store.scale_pools[i].data_ptr() if store.quant else None
+            L.kv_quant, L.kv_recip = int(store.quant), 0      # true division: the arithmetic of the reference's CPU decode
         store.native_layers = arr
         return arr
 
@@ -285,7 +288,10 @@ class Gpt2Engine:
                 att = att.view(B * S, C)
             else:
                 kv.write_packed(li, qkv, B, S, t0)
-                if S == 1:
+                if S == 1 and kv.scale_pool(li) is not None:
+                    att = ops.attn_decode_q8(qkv, kv.pool(li), kv.scale_pool(li), kv.block_table, B, H, C // H, t0 + 1,
+                                             scratch=kv.scratch)
+                elif S == 1:
                     att = ops.attn_decode(qkv, kv.pool(li), kv.block_table, B, H, C // H, t0 + 1, scratch=kv.scratch)
                 else:
                     if t0 != 0:

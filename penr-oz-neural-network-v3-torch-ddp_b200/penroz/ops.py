@@ -63,6 +63,24 @@ def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=Non
     return (out, out2) if epilogue == EPI_GELU else out
 
 
+def kv_append_q8(qkv2d, codes, scales, block_table, B, S, H, D, t0, writeback=False, recip_scale=False):
+    """Quantise the K and V columns of S new rows per sequence into the int8 page pool (+ per-token scales)."""
+    lib().kv_append_q8(ptr(qkv2d), ptr(codes), ptr(scales), ptr(block_table), block_table.shape[1], B, S, H, D, t0,
+                       dt(qkv2d), int(writeback), int(recip_scale), stream())
+
+
+def attn_decode_q8(qkv2d, codes, scales, block_table, B, H, D, t_len, scratch=None, out=None):
+    """Single-query attention over the int8 cache, de-quantising inside the kernel. Returns [B, H*D]."""
+    if out is None:
+        out = torch.empty((B, H * D), device=qkv2d.device, dtype=qkv2d.dtype)
+    need = lib().attn_decode_q8_scratch_bytes(B, H, D)
+    if scratch is None or scratch.numel() < need:
+        scratch = torch.empty(need, device=qkv2d.device, dtype=torch.uint8)
+    lib().attn_decode_q8(ptr(qkv2d), ptr(codes), ptr(scales), ptr(block_table), block_table.shape[1], ptr(out), B, H, D,
+                         t_len, dt(qkv2d), ptr(scratch), scratch.numel(), stream())
+    return out
+
+
 def widen_tokens(src_i32, dst_i64):
     """int32 token ids -> int64, on the device (dst may be any int64 tensor with as many elements)."""
     lib().widen_tokens(ptr(src_i32), ptr(dst_i64), src_i32.numel(), stream())

@@ -504,3 +504,54 @@ def test_training_stats_gpu_path_equals_host_path(dev):
         else:
             assert a == b, (path, a, b)
     close(host, gpu, "stats")
+
+
+# ------------------------------------------------------------------ int8 KV cache kernels
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_int8_kv_cache_kernels_match_the_torch_class(dev, dtype):
+    """penroz_kv_append_q8 / penroz_attn_decode_q8 against TurboQuantKVCache's own torch arithmetic
+    (kv_cache.py:119-125,135): codes and scales torch.equal to _quantize run on CUDA tensors (recip_scale=1) and on CPU
+    tensors (recip_scale=0, what the reference service computes), the written-back K/V equal to _dequantize, and
+    decode attention over the int8 pages equal to SDPA over the de-quantised cache."""
+    from kv_cache import TurboQuantKVCache
+    from penroz import ops
+    torch.manual_seed(3)
+    B, S, H, D = 3, 70, 4, 64
+    C = H * D
+    qkv = (torch.randn(B * S, 3 * C, device=dev) * 1.7).to(dtype)
+    qkv[5, C:C + D] = 0                                     # an all-zero key row: scale falls back to 1
+    max_pages = 2
+    table = torch.arange(B * max_pages, dtype=torch.int32, device=dev).view(B, max_pages)
+
+    def rows(t):        # [B*S, C] column block -> [B, H, S, D]
+        return t.view(B, S, H, D).permute(0, 2, 1, 3)
+
+    for recip in (1, 0):
+        codes = torch.zeros(B * max_pages, 2, H, 64, D, device=dev, dtype=torch.int8)
+        scales = torch.zeros(B * max_pages, 2, H, 64, device=dev, dtype=dtype)
+        work = qkv.clone()
+        ops.kv_append_q8(work, codes, scales, table, B, S, H, D, 0, writeback=True, recip_scale=bool(recip))
+        for kv, lo in ((0, C), (1, 2 * C)):
+            src = rows(qkv[:, lo:lo + C])
+            want_q, want_s = TurboQuantKVCache._quantize(src if recip else src.cpu())
+            want_q, want_s = want_q.to(dev), want_s.to(dev)
+            got_q = codes.view(B, max_pages, 2, H, 64, D)[:, :, kv].permute(0, 2, 1, 3, 4).reshape(B, H, 128, D)[:, :, :S]
+            got_s = scales.view(B, max_pages, 2, H, 64)[:, :, kv].permute(0, 2, 1, 3).reshape(B, H, 128)[:, :, :S]
+            assert torch.equal(got_q, want_q), (recip, kv)
+            assert torch.equal(got_s.unsqueeze(-1), want_s), (recip, kv)
+            deq = TurboQuantKVCache._dequantize(want_q, want_s)               # fp32
+            back = rows(work[:, lo:lo + C])
+            assert torch.equal(back.float(), deq.to(dtype).float())
+        assert torch.equal(work[:, :C], qkv[:, :C])                             # queries untouched
+    # decode attention: one new token per sequence at position S (second page), q8 cache vs SDPA on the de-quantised cache
+    new = (torch.randn(B, 3 * C, device=dev) * 1.7).to(dtype)
+    ops.kv_append_q8(new, codes, scales, table, B, 1, H, D, S, writeback=False, recip_scale=False)
+    out = ops.attn_decode_q8(new, codes, scales, table, B, H, D, S + 1)
+    k_all = (codes.view(B, max_pages, 2, H, 64, D)[:, :, 0].permute(0, 2, 1, 3, 4).reshape(B, H, 128, D)[:, :, :S + 1].float()
+             * scales.view(B, max_pages, 2, H, 64)[:, :, 0].permute(0, 2, 1, 3).reshape(B, H, 128)[:, :, :S + 1].float().unsqueeze(-1))
+    v_all = (codes.view(B, max_pages, 2, H, 64, D)[:, :, 1].permute(0, 2, 1, 3, 4).reshape(B, H, 128, D)[:, :, :S + 1].float()
+             * scales.view(B, max_pages, 2, H, 64)[:, :, 1].permute(0, 2, 1, 3).reshape(B, H, 128)[:, :, :S + 1].float().unsqueeze(-1))
+    q = new[:, :C].float().view(B, H, 1, D)
+    want = F.scaled_dot_product_attention(q, k_all, v_all).reshape(B, C)
+    tol = 1e-5 if dtype == torch.float32 else 2 ** -7
+    assert (out.float() - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
