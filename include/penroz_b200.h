@@ -221,16 +221,26 @@ int penroz_skinny_linear(const void* x, long long ldx, const void* W, long long 
                          long long ldo, const void* aux, long long ldaux, float* out_f32, long long ldo32, int M,
                          int N, int K, int epilogue, int flags, int dtype, void* stream);
 int penroz_argmax_rows(const void* x, long long ld, int rows, int V, long long* out, int dtype, void* stream);
+/* Weight-streaming Linear for 1 <= M <= 64 activation rows, bf16: out[M,N] = epi(LN?(x)[M,K] W[N,K]^T + bias).
+ * Replaces nn.Linear inside the generation loop (mappers.py:156-172 run at neural_net_model.py:465-469) together with
+ * the LayerNorm in front of it (ln_w != NULL: nn.LayerNorm with ln_eps, mappers.py:155,162,171), the GELU behind it
+ * (epilogue 1; flags bit0 = tanh form) or the residual add (epilogue 2, aux; neural_net_layers.py:130-135). Units of 16
+ * weight rows are dealt to every SM, the products run on mma.sync m16n8k16 (weights on the M side), every weight byte
+ * is read once with 16-byte loads issued before the activations are waited for. K % 32 == 0; LayerNorm needs K <= 2048. */
+int penroz_wstream_linear(const void* x, long long ldx, const void* W, long long ldw, const void* bias, void* out,
+                          long long ldo, const void* aux, long long ldaux, const void* ln_w, const void* ln_b,
+                          float ln_eps, int M, int N, int K, int epilogue, int flags, void* stream);
 
 /* ---- one whole single-token decode step of a GPT-2 tree, enqueued with a single host call ----
  * Replaces one iteration of the generation loop (neural_net_model.py:465-469, incremental branch :382-386): embedding
  * at position `pos`, every block (LN, QKV, paged K/V append at `pos`, split-KV attention over pos+1 keys, proj+residual,
  * LN, fc+GELU, proj2+residual), final LN, LM head into logits_out [B,V] (model dtype) and, when argmax_out is not NULL,
  * the greedy token ids. `layers` is a HOST array; every pointer inside it is a device pointer.
- * For B <= 8 the step runs as five launches per block (decode_fused.cu): LayerNorm, bias, GELU, residual and the K/V
- * page write ride in the prologue / epilogue of weight-streaming GEMV kernels, the split-KV attention merges its
- * partials inside a thread-block cluster, and consecutive launches overlap through programmatic dependent launch;
- * larger batches take one kernel per op with tensor-core GEMMs. Same results up to summation order. */
+ * The step runs as five launches per block (decode_fused.cu): LayerNorm, bias, GELU, residual and the K/V page write
+ * ride in the prologue / epilogue of weight-streaming Linear kernels (bf16, B <= 64: penroz_wstream_linear's kernel;
+ * fp32, B <= 8: an FP32-pipe GEMV), the split-KV attention merges its partials inside a thread-block cluster, and
+ * consecutive launches overlap through programmatic dependent launch; larger batches, and the int8 cache, take one
+ * kernel per op. Same results up to summation order. */
 typedef struct penroz_gpt2_layer_t {
     const void *ln1_w, *ln1_b, *qkv_w, *qkv_b, *proj_w, *proj_b, *ln2_w, *ln2_b, *fc_w, *fc_b, *proj2_w, *proj2_b;
     void* kv_pool;

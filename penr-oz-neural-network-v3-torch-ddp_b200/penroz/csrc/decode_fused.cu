@@ -17,6 +17,7 @@
 // Reference behaviour replaced: one iteration of neural_net_model.py:465-469 with the cache branch of
 // neural_net_layers.py:83-92 and kv_cache.py:41-68.
 #include "common.cuh"
+#include "wstream.cuh"
 #include <string.h>
 #include <stdlib.h>
 
@@ -576,6 +577,38 @@ static int launch_gemv(const GemvParams& p, int pro, cudaStream_t st) {
     return launch_gemv_mb<T, 8>(p, pro, st);
 }
 
+// bf16 Linears of the step go through the weight-streaming kernel (wstream.cu: 16-row units over every SM, mma.sync,
+// any batch up to 64); fp32 models and PENROZ_DECODE_WSTREAM=0 keep the FP32-pipe GEMV above (batch <= 8).
+static bool use_wstream() {
+    static const bool on = !(getenv("PENROZ_DECODE_WSTREAM") && !strcmp(getenv("PENROZ_DECODE_WSTREAM"), "0"));
+    return on;
+}
+template <typename T> struct IsBf16 { static constexpr bool value = false; };
+template <> struct IsBf16<__nv_bfloat16> { static constexpr bool value = true; };
+
+template <typename T>
+static int launch_linear(const GemvParams& p, int pro, cudaStream_t st) {
+    if (IsBf16<T>::value && use_wstream() && pro != PRO_COMBINE && wstream_supported(p.M, p.N, p.K, BF16) &&
+        (pro != PRO_LN || p.K <= 2048)) {
+        WsParams w{};
+        w.x = (const __nv_bfloat16*)p.x; w.ldx = p.ldx; w.W = (const __nv_bfloat16*)p.W; w.ldw = p.ldw;
+        w.bias = (const __nv_bfloat16*)p.bias; w.out = (__nv_bfloat16*)p.out; w.ldo = p.ldo;
+        w.aux = (const __nv_bfloat16*)p.aux; w.ldaux = p.ldaux;
+        w.M = p.M; w.N = p.N; w.K = p.K; w.epi = p.epi; w.gelu_tanh = p.gelu_tanh;
+        w.ln = pro == PRO_LN; w.ln_w = (const __nv_bfloat16*)p.ln_w; w.ln_b = (const __nv_bfloat16*)p.ln_b; w.ln_eps = p.ln_eps;
+        w.pool = (__nv_bfloat16*)p.pool; w.bt = p.bt; w.max_pages = p.max_pages; w.pos = p.pos; w.C = p.C; w.H = p.H; w.D = p.D;
+        w.amax_val = p.amax_val; w.amax_idx = p.amax_idx;
+        return launch_wstream(w, st);
+    }
+    PENROZ_REQUIRE(p.M <= 8, "decode step: %d activation rows need the weight-streaming kernel (bf16, K %% 32 == 0)", p.M);
+    return launch_gemv<T>(p, pro, st);
+}
+template <typename T>
+static int linear_candidates(int M, int N, int K) {
+    if (IsBf16<T>::value && use_wstream() && wstream_supported(M, N, K, BF16) && K <= 2048) return wstream_grid(M, N);
+    return gemv_candidates<T>(M, N);
+}
+
 static int fused_splits(int B, int H, int t_len) {
     int want = (2 * num_sms() + B * H - 1) / (B * H);
     const int maxs = (t_len + 31) / 32;
@@ -590,7 +623,9 @@ static int small_batch_limit() {   // PENROZ_DECODE_SMALL_MAX overrides the larg
     return v;
 }
 bool decode_small_supported(int B, int C, int H, int dtype) {
-    if (B > small_batch_limit() || C % H) return false;
+    const bool stream = dtype == BF16 && use_wstream() && C % 32 == 0 && !getenv("PENROZ_DECODE_SMALL_MAX") &&
+                        !(getenv("PENROZ_DECODE_ATTN") && !strcmp(getenv("PENROZ_DECODE_ATTN"), "split"));
+    if (B > (stream ? 64 : small_batch_limit()) || C % H) return false;
     const int D = C / H, vn = (dtype == F32) ? 4 : 8;
     if (D % vn) return false;
     const int lpk = D / vn;
@@ -672,7 +707,7 @@ static int decode_step_small_t(const long long* tokens, const void* wte, const v
         p.M = B; p.N = 3 * C; p.K = C; p.epi = 0;
         p.ln_w = L.ln1_w; p.ln_b = L.ln1_b; p.ln_eps = L.ln1_eps;
         p.pool = L.kv_pool; p.bt = block_table; p.max_pages = max_pages; p.pos = pos; p.C = C; p.H = H; p.D = D;
-        if ((rc = launch_gemv<T>(p, PRO_LN, st))) return rc;
+        if ((rc = launch_linear<T>(p, PRO_LN, st))) return rc;
         // split-KV attention over the pages (current token included)
         {
             cudaLaunchConfig_t cfg = {};
@@ -709,27 +744,27 @@ static int decode_step_small_t(const long long* tokens, const void* wte, const v
         p.x = att; p.ldx = C;
         p.W = L.proj_w; p.ldw = C; p.bias = L.proj_b; p.out = xo; p.ldo = C; p.aux = x; p.ldaux = C;
         p.M = B; p.N = C; p.K = C; p.epi = 2; p.part = part; p.splits = splits; p.H = H; p.D = D;
-        if ((rc = launch_gemv<T>(p, use_cluster ? PRO_PLAIN : PRO_COMBINE, st))) return rc;
+        if ((rc = launch_linear<T>(p, use_cluster ? PRO_PLAIN : PRO_COMBINE, st))) return rc;
         // LN2 + fc + GELU
         p = GemvParams{};
         p.x = xo; p.ldx = C; p.W = L.fc_w; p.ldw = C; p.bias = L.fc_b; p.out = g; p.ldo = L.ffn;
         p.M = B; p.N = L.ffn; p.K = C; p.epi = 1; p.gelu_tanh = L.gelu_tanh;
         p.ln_w = L.ln2_w; p.ln_b = L.ln2_b; p.ln_eps = L.ln2_eps;
-        if ((rc = launch_gemv<T>(p, PRO_LN, st))) return rc;
+        if ((rc = launch_linear<T>(p, PRO_LN, st))) return rc;
         // proj2 + residual
         p = GemvParams{};
         p.x = g; p.ldx = L.ffn; p.W = L.proj2_w; p.ldw = L.ffn; p.bias = L.proj2_b; p.out = x; p.ldo = C;
         p.aux = xo; p.ldaux = C; p.M = B; p.N = C; p.K = L.ffn; p.epi = 2;
-        if ((rc = launch_gemv<T>(p, PRO_PLAIN, st))) return rc;
+        if ((rc = launch_linear<T>(p, PRO_PLAIN, st))) return rc;
     }
     // final LN + LM head (+ per-CTA arg-max candidates)
     GemvParams p{};
     p.x = x; p.ldx = C; p.W = head_w; p.ldw = C; p.bias = head_b; p.out = logits_out; p.ldo = V;
     p.M = B; p.N = V; p.K = C; p.epi = 0; p.ln_w = lnf_w; p.ln_b = lnf_b; p.ln_eps = lnf_eps;
-    const int nblk = gemv_candidates<T>(B, V);
+    const int nblk = linear_candidates<T>(B, V, C);
     const bool fused_amax = argmax_out && nblk <= kAmaxSlots;
     if (fused_amax) { p.amax_val = amax_val; p.amax_idx = amax_idx; }
-    if ((rc = launch_gemv<T>(p, PRO_LN, st))) return rc;
+    if ((rc = launch_linear<T>(p, PRO_LN, st))) return rc;
     if (fused_amax) {
         argmax_candidates_kernel<<<B, 256, 0, st>>>(amax_val, amax_idx, nblk, argmax_out);
         count_launch();

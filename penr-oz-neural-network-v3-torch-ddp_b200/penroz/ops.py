@@ -81,6 +81,17 @@ def attn_decode_q8(qkv2d, codes, scales, block_table, B, H, D, t_len, scratch=No
     return out
 
 
+def wstream_linear(x, W, bias=None, epilogue=0, aux=None, tanh=False, ln_w=None, ln_b=None, ln_eps=1e-5):
+    """Weight-streaming Linear (decode, bf16, M <= 64 rows): epi(LN?(x) W^T + bias). epilogue 0 store, 1 GELU, 2 residual."""
+    M, K = x.shape
+    N = W.shape[0]
+    out = torch.empty((M, N), device=x.device, dtype=x.dtype)
+    lib().wstream_linear(ptr(x), x.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(out), N, ptr(aux),
+                         aux.stride(0) if aux is not None else 0, ptr(ln_w), ptr(ln_b), float(ln_eps), M, N, K,
+                         int(epilogue), int(bool(tanh)), stream())
+    return out
+
+
 def widen_tokens(src_i32, dst_i64):
     """int32 token ids -> int64, on the device (dst may be any int64 tensor with as many elements)."""
     lib().widen_tokens(ptr(src_i32), ptr(dst_i64), src_i32.numel(), stream())

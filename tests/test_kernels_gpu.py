@@ -555,3 +555,37 @@ def test_int8_kv_cache_kernels_match_the_torch_class(dev, dtype):
     want = F.scaled_dot_product_attention(q, k_all, v_all).reshape(B, C)
     tol = 1e-5 if dtype == torch.float32 else 2 ** -7
     assert (out.float() - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+
+
+# ------------------------------------------------------------------ weight-streaming Linear of the decode step
+@pytest.mark.parametrize("M", [1, 5, 8, 16, 33, 64])
+def test_wstream_linear(dev, M):
+    """penroz_wstream_linear (mma.sync, 16-row units, LayerNorm / GELU / residual fused) against torch on the same
+    bf16 inputs with fp32 accumulation: plain, LN + bias, GELU (erf and tanh), residual with a long reduction, and a row
+    count that is not a multiple of 16 (the LM head's 50257)."""
+    from penroz import ops
+    torch.manual_seed(M)
+    bf = torch.bfloat16
+
+    def rnd(*shape, s=1.0):
+        return (torch.randn(*shape, device=dev) * s).to(bf)
+    cases = [(768, 2304, 0, True), (768, 3072, 1, True), (3072, 768, 2, False), (768, 50257, 0, True), (1600, 4800, 1, True),
+             (768, 768, 2, False)]
+    for K, N, epi, ln in cases:
+        x, W, b = rnd(M, K), rnd(N, K, s=0.03), rnd(N, s=0.1)
+        aux = rnd(M, N) if epi == 2 else None
+        g, be = (1 + rnd(K, s=0.1)), rnd(K, s=0.1)
+        xin = x.float()
+        if ln:
+            xin = F.layer_norm(xin, (K,), g.float(), be.float(), 1e-5).to(bf).float()
+        want = (xin @ W.float().t() + b.float()).to(bf).float()
+        for tanh in ((False, True) if epi == 1 else (False,)):
+            w2 = want
+            if epi == 1:
+                w2 = F.gelu(want, approximate="tanh" if tanh else "none").to(bf).float()
+            elif epi == 2:
+                w2 = (aux.float() + want).to(bf).float()
+            got = ops.wstream_linear(x, W, b, epilogue=epi, aux=aux, tanh=tanh, ln_w=g if ln else None,
+                                     ln_b=be if ln else None).float()
+            scale = max(1.0, w2.abs().max().item())
+            assert (got - w2).abs().max().item() <= 2 ** -7 * scale, (K, N, epi, ln, tanh, (got - w2).abs().max().item())
