@@ -236,6 +236,8 @@ int penroz_wstream_linear(const void* x, long long ldx, const void* W, long long
  * at position `pos`, every block (LN, QKV, paged K/V append at `pos`, split-KV attention over pos+1 keys, proj+residual,
  * LN, fc+GELU, proj2+residual), final LN, LM head into logits_out [B,V] (model dtype) and, when argmax_out is not NULL,
  * the greedy token ids. `layers` is a HOST array; every pointer inside it is a device pointer.
+ * With PENROZ_DECODE_MEGA=1 (bf16, B <= 64, n_embd <= 1024) the whole step is ONE persistent cooperative kernel
+ * (decode_mega.cu; measured slower than the default on B200, kept as an experiment). By default:
  * The step runs as five launches per block (decode_fused.cu): LayerNorm, bias, GELU, residual and the K/V page write
  * ride in the prologue / epilogue of weight-streaming Linear kernels (bf16, B <= 64: penroz_wstream_linear's kernel;
  * fp32, B <= 8: an FP32-pipe GEMV), the split-KV attention merges its partials inside a thread-block cluster, and
@@ -249,6 +251,9 @@ typedef struct penroz_gpt2_layer_t {
     void* kv_scales;        /* int8 cache (kv_quant != 0): kv_pool holds int8 codes, this the per-token scales; else NULL */
     int kv_quant, kv_recip; /* kv_recip: see penroz_kv_append_q8's recip_scale */
 } penroz_gpt2_layer_t;
+/* The workspace must be ZERO when it is first handed to penroz_gpt2_decode_step (its head holds the persistent
+ * kernel's barrier and per-head counters); every step leaves those words zero again, so one cudaMemset at allocation
+ * is enough. A workspace is used by one step at a time (steps on one stream; one workspace per concurrent generation). */
 size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F, int t_len_max);
 /* The prompt pass that starts a generation (neural_net_model.py:387-390 with an empty cache): all S positions through
  * every block with K/V appended at positions 0..S-1, final LayerNorm + LM head on the last position of each sequence

@@ -393,10 +393,20 @@ int decode_step_small(const long long* tokens, const void* wte, const void* wpe,
                       void* logits_out, long long* argmax_out, int* err_flag, cudaStream_t st);
 }
 
+namespace penroz {   // decode_mega.cu: the whole step as one persistent cooperative kernel (bf16, batch <= 64)
+bool decode_mega_supported(int B, int C, int H, int V, int F, int n_layer, int dtype);
+size_t decode_mega_extra_bytes(int B, int H);
+int decode_step_mega(const long long* tokens, const void* wte, const void* wpe, const penroz_gpt2_layer_t* layers,
+                     int n_layer, const void* lnf_w, const void* lnf_b, float lnf_eps, const void* head_w,
+                     const void* head_b, const int* block_table, int max_pages, int B, int C, int H, int V, int pos,
+                     void* xa, void* xb, void* qkv, void* att, void* g, float* part, float* amax_val, int* amax_idx,
+                     unsigned* sync, void* logits_out, long long* argmax_out, int* err_flag, cudaStream_t st);
+}
+
 extern "C" size_t penroz_gpt2_decode_workspace_bytes(int B, int C, int H, int F, int t_len_max) {
     const size_t es = 4;  // sized for fp32; bf16 uses half of the activation part
     const size_t act = (size_t)B * ((size_t)2 * C + C + 3 * C + C + 2 * (size_t)F + C) * es + 8 * 256;
-    return act + penroz_attn_decode_scratch_bytes(B, H, C / H, t_len_max) + 256 +
+    return decode_mega_extra_bytes(B, H) + act + penroz_attn_decode_scratch_bytes(B, H, C / H, t_len_max) + 256 +
            decode_small_extra_bytes(B);
 }
 
@@ -416,6 +426,8 @@ extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte,
     const int D = C / H;
     const size_t es = dtype == F32 ? 4 : 2;
     uint8_t* w = (uint8_t*)workspace;
+    unsigned* sync_words = (unsigned*)w;          // zero when the workspace is handed over, left zero by every step
+    w += decode_mega_extra_bytes(B, H);
     auto carve = [&](size_t elems) { void* p = w; w += ((elems * es + 255) / 256) * 256; return p; };
     void* xa = carve((size_t)B * C);
     void* xb = carve((size_t)B * C);
@@ -426,7 +438,15 @@ extern "C" int penroz_gpt2_decode_step(const long long* tokens, const void* wte,
     void* hpre = carve((size_t)B * F);
     void* attn_scratch = w;
     const size_t attn_scratch_bytes = penroz_attn_decode_scratch_bytes(B, H, D, pos + 1);
-    const bool q8 = layers[0].kv_quant != 0;      // int8 cache: one kernel per op, quantise-on-append + dequantising attention
+    const bool q8 = layers[0].kv_quant != 0;
+    if (!q8 && !getenv("PENROZ_DECODE_UNFUSED") && decode_mega_supported(B, C, H, V, F, n_layer, dtype)) {
+        uint8_t* extra = w + ((attn_scratch_bytes + 255) / 256) * 256;
+        float* amax_val = (float*)extra;
+        int* amax_idx = (int*)(amax_val + (size_t)B * 16384);
+        return decode_step_mega(tokens, wte, wpe, layers, n_layer, lnf_w, lnf_b, lnf_eps, head_w, head_b, block_table,
+                                max_pages, B, C, H, V, pos, xa, xb, qkv, att, g, (float*)attn_scratch, amax_val,
+                                amax_idx, sync_words, logits_out, argmax_out, err_flag, (cudaStream_t)stream);
+    }      // int8 cache: one kernel per op, quantise-on-append + dequantising attention
     if (!q8 && decode_small_supported(B, C, H, dtype) && !getenv("PENROZ_DECODE_UNFUSED")) {
         void* extra = w + ((attn_scratch_bytes + 255) / 256) * 256;
         return decode_step_small(tokens, wte, wpe, layers, n_layer, lnf_w, lnf_b, lnf_eps, head_w, head_b, block_table,

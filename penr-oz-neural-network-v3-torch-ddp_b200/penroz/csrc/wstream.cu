@@ -57,8 +57,10 @@ int ws_nt(int M) { return M <= 8 ? 1 : (M <= 16 ? 2 : (M <= 32 ? 4 : 8)); }
 // CTAs the launch uses for N output columns (= arg-max candidates per row)
 int wstream_grid(int M, int N) {
     const int nunits = (N + 15) / 16;
-    const int per_sm = ws_nt(M) >= 4 ? 1 : 2;        // shared memory per CTA grows with the staged rows
-    const int cap = num_sms() * per_sm;
+    // measured at batch 1 (124M head, 3142 units): 4 CTAs per SM's worth of shorter unit loops beat one resident CTA per
+    // SM looping 21 times (322 vs 369 us per token step), although the extra CTAs run as later waves
+    static const int small_per_sm = getenv("PENROZ_WS_PER_SM") ? atoi(getenv("PENROZ_WS_PER_SM")) : 1;
+    const int cap = num_sms() * (ws_nt(M) >= 4 ? 1 : small_per_sm);
     return nunits < cap ? nunits : cap;
 }
 

@@ -91,7 +91,7 @@ __device__ __forceinline__ void ws_prefetch_first(const WsParams& p, int kchunk,
 // load independent of the others; rows >= M are zero. With p.ln (needs k0 == 0 and kc == K) LayerNorm is applied in
 // place afterwards, one warp per row out of shared memory. Ends with a barrier.
 template <int NT>
-__device__ __noinline__ void ws_stage_rows_general(const WsParams& p, __nv_bfloat16* xs, int xstride, int k0, int kc) {
+__device__ __forceinline__ void ws_stage_rows_general_impl(const WsParams& p, __nv_bfloat16* xs, int xstride, int k0, int kc) {
     constexpr int MB = 8 * NT;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int kv8 = kc >> 3, total = MB * kv8;
@@ -297,10 +297,18 @@ __device__ __noinline__ void ws_stage_rows_general(const WsParams& p, __nv_bfloa
     }
 }
 
+template <int NT>
+__device__ __noinline__ void ws_stage_rows_general(const WsParams& p, __nv_bfloat16* xs, int xstride, int k0, int kc) {
+    ws_stage_rows_general_impl<NT>(p, xs, xstride, k0, kc);
+}
+
 // The common case inline (plain rows, or LayerNorm over rows of at most 1024 columns staged whole); embedding rows,
 // LayerNorm over longer or chunk-staged rows go through the general routine above.
 template <int NT>
 __device__ __forceinline__ void ws_stage_rows(const WsParams& p, __nv_bfloat16* xs, int xstride, int k0, int kc) {
+    // few rows (NT < 4): LayerNorm out of shared memory in the general routine -- it keeps this kernel's register count low
+    // enough for several CTAs per SM, which is what keeps enough weight bytes in flight at small batch
+    if (NT < 4) { ws_stage_rows_general_impl<NT>(p, xs, xstride, k0, kc); return; }     // small kernels: all inline
     if (p.tok || (p.ln && (kc < p.K || p.K > 1024))) { ws_stage_rows_general<NT>(p, xs, xstride, k0, kc); return; }
     constexpr int MB = 8 * NT;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

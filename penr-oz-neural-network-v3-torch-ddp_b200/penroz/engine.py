@@ -210,7 +210,7 @@ class Gpt2Engine:
         need = ops.lib().gpt2_decode_workspace_bytes(B, C, H, F, pl.block_size)
         ws = getattr(store, "native_ws", None)
         if ws is None or ws.numel() < need:
-            ws = store.native_ws = torch.empty(need, device=self.device, dtype=torch.uint8)
+            ws = store.native_ws = torch.zeros(need, device=self.device, dtype=torch.uint8)   # zeroed once: holds the step's barrier words
         dt = pl.wte.weight.dtype
         logits = torch.empty((B, 1, V), device=self.device, dtype=dt)
         ids = torch.empty((B, 1), device=self.device, dtype=torch.int64)

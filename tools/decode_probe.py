@@ -38,3 +38,25 @@ for B in Bs:
         t_host = time.perf_counter() - t0
         torch.cuda.synchronize()
     print(f"B={B}: GPU {e0.elapsed_time(e1) / steps * 1e3:.1f} us/step, host enqueue {t_host / steps * 1e6:.1f} us/step", flush=True)
+    if os.environ.get("PROBE_GRAPH"):
+        # the same step replayed from a CUDA graph (fixed position: timing only): what is left when the host and the
+        # launch path are out of the picture
+        side = torch.cuda.Stream()
+        with torch.inference_mode(), torch.cuda.stream(side):
+            kv.commit(-1)
+            eng.decode_step(ids, 1000, kv)
+            kv.commit(-1)
+            side.synchronize()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=side):
+                eng.decode_step(ids, 1000, kv)
+            kv.commit(-1)
+            side.synchronize()
+            gr.replay()
+            side.synchronize()
+            e0.record(side)
+            for i in range(steps):
+                gr.replay()
+            e1.record(side)
+            side.synchronize()
+        print(f"B={B}: graph replay {e0.elapsed_time(e1) / steps * 1e3:.1f} us/step", flush=True)
