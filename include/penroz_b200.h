@@ -13,7 +13,11 @@
  *   - no entry point allocates, frees or synchronises unless its comment says so; work is enqueued on `stream`
  *     (a cudaStream_t passed as void*);
  *   - dtype codes: 0 = float32, 1 = bfloat16; matrices are row-major with a leading dimension in ELEMENTS;
- *   - the library is re-entrant (no mutable globals besides a launch counter and per-thread error text).
+ *   - the library is re-entrant: calls on any number of host threads and streams are independent. Its mutable globals
+ *     are a launch counter, per-thread error text, and two pieces of device-resident state named where they are used:
+ *     the tile-counter pairs of penroz_gemm_bf16 (1024 pairs, one dealt per call, reset by the call's last CTA; a
+ *     launch that dies mid-kernel can leave its pair non-zero -- after a CUDA error the process should not go on
+ *     using the library) and the fixed scratch array of penroz_colsum_static (calls sharing a device must not overlap).
  */
 #ifndef PENROZ_B200_H
 #define PENROZ_B200_H

@@ -326,7 +326,8 @@ class NeuralNetworkModel(nn.Module):
         # in the layers' forward: only the module composition honours it. The fused decode step never comes through
         # here -- _generate_next_token drives the engine directly with its paged cache.
         cache_attached = any(layer._kv_cache is not None for layer in self._find_attention_layers())
-        if engine is not None and input_tensor.is_cuda and not input_tensor.is_floating_point() and not cache_attached:
+        if (engine is not None and input_tensor.is_cuda and not input_tensor.is_floating_point() and not cache_attached
+                and not self.__dict__.get("_torch_training")):
             return self._forward_fused(engine, input_tensor, target, skip_softmax)
         run = self.layers[:-1] if (skip_softmax and self._is_softmax_last) else self.layers
         outputs = []
@@ -661,10 +662,20 @@ class NeuralNetworkModel(nn.Module):
             last_saved = time.time()
 
         engine = self._engine() if device.type == 'cuda' else None
+        if engine is not None and (engine.plan.active_dropout(True) or engine.param_mode() != "f32"):
+            # An HF-imported GPT-2 (bf16 parameters, dropout 0.1: neural_net_model.py:219-222, mappers.py:140-142) is
+            # outside what the fused step implements (fp32 master weights, no dropout: torch's Philox stream would have
+            # to be reproduced for parity). The reference trains such a model with plain torch; so does the drop-in --
+            # /import/ then /train/ keeps working -- and it says that this run is not the fused path.
+            if master:
+                log.warning(f"Model {self.model_id}: parameters are {engine.param_mode()} / dropout is active -- training "
+                            f"runs through torch autograd (the reference's own step), not the fused sm_100a step")
+            engine = None
         if engine is not None:
             stepper = _FusedStepper(self, engine, device, use_amp=(os.environ.get("PENROZ_TRAIN_PRECISION", "amp") != "f32"))
         else:
             stepper = _TorchStepper(self, device, amp_ctx, amp_scaler)
+        self.__dict__["_torch_training"] = isinstance(stepper, _TorchStepper)
         stepper.begin()
         if hasattr(stepper, "warn_if_ranks_will_drift"):
             stepper.warn_if_ranks_will_drift(num_steps)
@@ -684,6 +695,7 @@ class NeuralNetworkModel(nn.Module):
             try:
                 cost, pairs = stepper.run_epoch(loader, num_steps, batch_size, block_size, want_stats)
             except Exception as exc:
+                self.__dict__["_torch_training"] = False
                 if master:
                     log.error(f"Model {self.model_id}: Training Epoch {epoch + 1} failed: {str(exc)}")
                     self.status = _now_status("Error", f"Training epoch {epoch + 1} failed: {str(exc)}")
@@ -712,6 +724,7 @@ class NeuralNetworkModel(nn.Module):
                 self.serialize()
                 last_saved = time.time()
         stepper.end()
+        self.__dict__["_torch_training"] = False
         if master:
             self.status = _now_status("Trained", f"Model trained for {epochs} epochs.")
             log.info(f"Model {self.model_id}: Done training for {epochs} epochs.")

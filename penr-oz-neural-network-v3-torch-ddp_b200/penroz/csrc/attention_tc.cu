@@ -268,26 +268,38 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                 }
             }
             float ls = 0.f;
-            // pass 2: p = 2^(s*scale*log2e - mn), partial row sum, P -> smem (bf16, swizzled K-major)
+            // pass 2: p = 2^(s*scale*log2e - mn), partial row sum, P -> smem (bf16, swizzled K-major). Off the
+            // diagonal tile (all but one tile per row of tiles) there is no mask: per pair of scores 2 FFMA, 2 MUFU.EX2,
+            // one pack and 2 FADD -- the row sum adds the fp32 probabilities (as torch's softmax does before its own
+            // rounding); the kernel was issue-bound at 9 instructions per score with the mask selects and the bf16
+            // round trip of the sum in every tile.
+            const float neg_mn = -mn;
 #pragma unroll 1
             for (int c = 0; c < 2; ++c) {
                 uint32_t v[32];
                 tmem_ld_32x32(tS + lane_addr + half * 64 + c * 32, v);
                 tmem_ld_wait();
                 uint32_t packed[16];
+                if (!diag) {
+                    float ls0 = 0.f, ls1 = 0.f;
 #pragma unroll
-                for (int k = 0; k < 32; k += 2) {
-                    float pa = ex2_fast(fmaf(__uint_as_float(v[k]), scale_log2e, -mn));
-                    float pb = ex2_fast(fmaf(__uint_as_float(v[k + 1]), scale_log2e, -mn));
-                    if (diag) {
+                    for (int k = 0; k < 32; k += 2) {
+                        const float pa = ex2_fast(fmaf(__uint_as_float(v[k]), scale_log2e, neg_mn));
+                        const float pb = ex2_fast(fmaf(__uint_as_float(v[k + 1]), scale_log2e, neg_mn));
+                        ls0 += pa; ls1 += pb;
+                        packed[k >> 1] = pack_bf16x2(pa, pb);
+                    }
+                    ls += ls0 + ls1;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 32; k += 2) {
+                        float pa = ex2_fast(fmaf(__uint_as_float(v[k]), scale_log2e, neg_mn));
+                        float pb = ex2_fast(fmaf(__uint_as_float(v[k + 1]), scale_log2e, neg_mn));
                         if (key0 + c * 32 + k > i) pa = 0.f;
                         if (key0 + c * 32 + k + 1 > i) pb = 0.f;
+                        ls += pa + pb;
+                        packed[k >> 1] = pack_bf16x2(pa, pb);
                     }
-                    // the row sum uses the bf16-rounded probabilities the PV product will see
-                    __nv_bfloat162 hb = __floats2bfloat162_rn(pa, pb);
-                    float2 back = __bfloat1622float2(hb);
-                    ls += back.x + back.y;
-                    packed[k >> 1] = *reinterpret_cast<uint32_t*>(&hb);
                 }
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4)
@@ -561,18 +573,31 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 tmem_ld_32x32(tDP + lane_addr + part * 32, dv);
                 tmem_ld_wait();
                 uint32_t pp[16], dd[16];
+                // dS = P (dP - delta) scale with the scale folded into one FFMA: (dP - delta) scale = dP scale - delta scale.
+                // Interior tiles (no mask, all rows live) run a loop without selects: 5 instructions per score.
+                const float negL2 = -L2, ndl = -dl * scale;
+                if (!edge) {
 #pragma unroll
-                for (int k = 0; k < 32; k += 2) {
-                    float p0 = ex2_fast(fmaf(__uint_as_float(sv[k]), scale_log2e, -L2));
-                    float p1 = ex2_fast(fmaf(__uint_as_float(sv[k + 1]), scale_log2e, -L2));
-                    if (edge) {   // diagonal tile or a tile with rows past the sequence end: warp-uniform flag
+                    for (int k = 0; k < 32; k += 2) {
+                        const float p0 = ex2_fast(fmaf(__uint_as_float(sv[k]), scale_log2e, negL2));
+                        const float p1 = ex2_fast(fmaf(__uint_as_float(sv[k + 1]), scale_log2e, negL2));
+                        const float d0 = p0 * fmaf(__uint_as_float(dv[k]), scale, ndl);
+                        const float d1 = p1 * fmaf(__uint_as_float(dv[k + 1]), scale, ndl);
+                        pp[k >> 1] = pack_bf16x2(p0, p1);
+                        dd[k >> 1] = pack_bf16x2(d0, d1);
+                    }
+                } else {      // diagonal tile or a tile with rows past the sequence end
+#pragma unroll
+                    for (int k = 0; k < 32; k += 2) {
+                        float p0 = ex2_fast(fmaf(__uint_as_float(sv[k]), scale_log2e, negL2));
+                        float p1 = ex2_fast(fmaf(__uint_as_float(sv[k + 1]), scale_log2e, negL2));
                         if (!row_ok || (diag && key0 + k > i)) p0 = 0.f;
                         if (!row_ok || (diag && key0 + k + 1 > i)) p1 = 0.f;
+                        const float d0 = p0 * fmaf(__uint_as_float(dv[k]), scale, ndl);
+                        const float d1 = p1 * fmaf(__uint_as_float(dv[k + 1]), scale, ndl);
+                        pp[k >> 1] = pack_bf16x2(p0, p1);
+                        dd[k >> 1] = pack_bf16x2(d0, d1);
                     }
-                    const float d0 = p0 * (__uint_as_float(dv[k]) - dl) * scale;
-                    const float d1 = p1 * (__uint_as_float(dv[k + 1]) - dl) * scale;
-                    pp[k >> 1] = pack_bf16x2(p0, p1);
-                    dd[k >> 1] = pack_bf16x2(d0, d1);
                 }
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4) {

@@ -23,7 +23,7 @@ def test_c_abi_library_loads_and_exports_every_declared_symbol():
     lib = _lib.lib()                        # dlopen works without a GPU
     for name in protos:
         assert hasattr(lib._cdll, name), f"{name} declared in include/penroz_b200.h but not exported"
-    assert lib.abi_version() == 1 and lib.kv_page_size() == 64
+    assert lib.abi_version() == 2 and lib.kv_page_size() == 64
     assert lib.layernorm_bwd_scratch_bytes(32768, 768) > 0
     if not torch.cuda.is_available():
         with pytest.raises(_lib.PenrozError):
@@ -38,7 +38,7 @@ def test_argument_validation_without_a_gpu():
     with pytest.raises(_lib.PenrozError, match="head_dim"):
         lib.attn_fwd_tc(None, None, None, 1, 8, 1, 48, None)
     with pytest.raises(_lib.PenrozError, match="8192"):
-        lib.colsum_static(1, 8, 4, 9000, 1, 0, 0, None)
+        lib.colsum_static(1, 9000, 4, 9000, 1, 0, 0, None)
 
 
 def test_dsl_builds_the_reference_weights_from_the_same_seed(golden):

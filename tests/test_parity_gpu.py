@@ -499,3 +499,20 @@ def test_124m_bf16_greedy_ids_match_reference_cuda(env, golden_bf16):
         assert len(sampled) == len(g[f"decode/{tag}/topk50_seed42_ids"]) and sampled[:n_prompt] == want[:n_prompt]
         del m
         torch.cuda.empty_cache()
+
+
+def test_hf_import_style_model_trains_on_cuda(env, monkeypatch):
+    """/import/ then /train/ (neural_net_model.py:176-237 keeps imported checkpoints in bf16 and mappers.py:140-142 gives
+    them dropout 0.1): outside the fused step (fp32 master weights, p = 0), so like the reference the drop-in trains
+    it with torch autograd on the GPU instead of refusing -- losses finite and falling, status Trained, bf16 kept."""
+    m = build_gpt("hfstyle", 2, 4, 128, 64, 65, dropout=0.1)
+    m.to(dtype=torch.bfloat16)
+    m.to("cuda")
+    torch.manual_seed(3)
+    m.train_model("synth65", 0, 12, 16, 64, 16)
+    loss = [p["cost"] for p in m.progress]
+    assert m.status["code"] == "Trained" and len(loss) == 12 and all(np.isfinite(loss))
+    assert loss[-1] < loss[0]
+    assert next(m.parameters()).dtype == torch.bfloat16
+    # and the trained bf16 model still decodes on the fused path
+    assert len(m.generate_tokens([[1, 2, 3]], 64, 8, temperature=0.0)) == 11
