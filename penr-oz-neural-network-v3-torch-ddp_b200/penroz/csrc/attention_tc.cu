@@ -220,11 +220,88 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
         for (int d = 0; d < 32; ++d) o[d] = 0.f;
         float m = -INFINITY, l = 0.f;
         uint8_t* blk = smem + AttnFwdSmem::kP + half * 16384;   // this half's 64-key block of P
+        int* redo_flag = reinterpret_cast<int*>(sum_s + 256);   // 3 rotating CTA-wide flags (slack after the row sums)
+        if (threadIdx.x < 3) redo_flag[threadIdx.x] = 0;
+        softmax_pair_sync();
         for (int j = 0; j < n_kv; ++j) {
             mbar_wait(s_full, (uint32_t)(j & 1));
             tc_fence_after();
             const bool diag = (j == qt);
             const int key0 = j * AT_BN + half * 64;
+            if (LAZY && j > 0) {
+                // ---- ONE pass over S for every tile after the first: the exponent uses the running maximum as it stands
+                // (it may lag the tile's own maximum by up to 2^tau, which bf16 / fp32 hold easily), the tile's maximum
+                // is tracked on the side, and only if some row of the CTA outgrew its maximum by more than tau is the
+                // tile redone by the two-pass code below. S is read from tensor memory once instead of twice -- the
+                // kernel sat on TMEM read bandwidth (two 64 KB passes per 128x128 tile), not on the exponentials.
+                if (threadIdx.x == 0) redo_flag[(j + 1) % 3] = 0;
+                const float neg_m = -m;
+                float mt = -INFINITY, ls = 0.f;
+#pragma unroll 1
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(tS + lane_addr + half * 64 + c * 32, v);
+                    tmem_ld_wait();
+                    uint32_t packed[16];
+                    if (!diag) {
+                        float ls0 = 0.f, ls1 = 0.f, m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+                        for (int k = 0; k < 32; k += 2) {
+                            const float sa = __uint_as_float(v[k]), sb = __uint_as_float(v[k + 1]);
+                            m0 = fmaxf(m0, sa); m1 = fmaxf(m1, sb);
+                            const float pa = ex2_fast(fmaf(sa, scale_log2e, neg_m));
+                            const float pb = ex2_fast(fmaf(sb, scale_log2e, neg_m));
+                            ls0 += pa; ls1 += pb;
+                            packed[k >> 1] = pack_bf16x2(pa, pb);
+                        }
+                        ls += ls0 + ls1;
+                        mt = fmaxf(mt, fmaxf(m0, m1));
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 32; k += 2) {
+                            const bool oka = key0 + c * 32 + k <= i, okb = key0 + c * 32 + k + 1 <= i;
+                            const float sa = __uint_as_float(v[k]), sb = __uint_as_float(v[k + 1]);
+                            if (oka) mt = fmaxf(mt, sa);
+                            if (okb) mt = fmaxf(mt, sb);
+                            const float pa = oka ? ex2_fast(fmaf(sa, scale_log2e, neg_m)) : 0.f;
+                            const float pb = okb ? ex2_fast(fmaf(sb, scale_log2e, neg_m)) : 0.f;
+                            ls += pa + pb;
+                            packed[k >> 1] = pack_bf16x2(pa, pb);
+                        }
+                    }
+                    if (c == 0) {
+                        // PV_{j-1} reads the P buffer about to be overwritten (and it is what a rescale would scale): it
+                        // was issued a whole S MMA ago and has normally retired while the first half was computed
+                        mbar_wait(o_full, (uint32_t)((j - 1) & 1));
+                        tc_fence_after();
+                    }
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4)
+                        *reinterpret_cast<uint4*>(blk + sw128_off(r, c * 32 + q4 * 8)) =
+                            make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
+                }
+                if (fmaf(mt, scale_log2e, neg_m) > kLazyTau) redo_flag[j % 3] = 1;
+                softmax_pair_sync();
+                if (redo_flag[j % 3] == 0) {
+                    tc_fence_before();
+                    fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(p_ready);
+                    l += ls;
+                    if (j == n_kv - 1) {
+                        mbar_wait(o_full, (uint32_t)(j & 1));
+                        tc_fence_after();
+                        uint32_t v[32];
+                        tmem_ld_32x32(tO + lane_addr + half * 32, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int k = 0; k < 32; ++k) o[k] = __uint_as_float(v[k]);
+                    }
+                    tc_fence_before();
+                    continue;
+                }
+                // some row jumped: fall through to the two-pass code, which rescales O and rewrites P for this tile
+            }
             // pass 1: maximum over this thread's 64 columns, then over the pair (mask only on the diagonal tile)
             float mt = -INFINITY;
 #pragma unroll 1
