@@ -38,6 +38,14 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int col) {
 }
 
 // ---------------------------------------------------------------------------------------------- forward
+// Where the forward stands (clock64 timeline of one CTA, B=32 T=1024 H=12, round 2): a key tile takes ~3,080 cycles per
+// CTA, two CTAs per SM. 2,080 of them are the exponential pass -- 64 MUFU.EX2 per thread on 16 SFU lanes per SM, which
+// both resident CTAs want at once -- and ~1,000 are the hand-off chain (P ready -> S_{j+1} issued, 8 tcgen05.mma at ~75
+// cycles of issue each -> S complete -> softmax wakes). The SFU is busy 66 % of the time: the two CTAs fall into
+// lock-step (they share the SFU fairly, finish their passes together and idle through the chain together). Packing two
+// exponentials per SFU operation (ex2.approx.f16x2) measured SLOWER (171 vs 153 us: the packed form is not double
+// rate and adds conversions). What is left is the two-tile ping-pong inside one CTA (explicitly alternating softmax
+// groups) and an FMA-pipe polynomial for part of the exponentials.
 struct AttnFwdSmem {
     // sized so that TWO CTAs fit in one SM's 227 KB (one CTA's softmax overlaps the other's MMAs): K is single
     // buffered (its only reader, the S MMA, retires long before the next K is needed), V double buffered
