@@ -52,8 +52,7 @@ struct AttnFwdSmem {
     static constexpr int kQ = 0;                     // 16 KB
     static constexpr int kK0 = 16384;                // 16 KB
     static constexpr int kV0 = kK0 + 16384;          // 2 stages x 16 KB
-    static constexpr int kP = kV0 + 2 * 16384;       // 32 KB: [2 key blocks][128 rows][64]
-    static constexpr int kBar = kP + 32768;          // 128 B of barriers + tmem slot
+    static constexpr int kBar = kV0 + 2 * 16384;     // 128 B of barriers + tmem slot (P lives in tensor memory)
     static constexpr int kMax = kBar + 128;          // [2 parity][2 halves][128 rows] floats: row-max exchange
     static constexpr int kSum = kMax + 2048;         // [2 halves][128 rows] floats: final row-sum exchange
     static constexpr int kBytes = kSum + 1024 + 1024;  // + alignment slack
@@ -109,12 +108,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
-    const uint32_t tS = tmem, tO = tmem + 128;
+    // S [0,128) fp32 | P [128,192): the probabilities as bf16 pairs, the A operand of the PV product read straight from
+    // tensor memory (no shared-memory round trip: the kernel was bound by shared-memory bandwidth, which the MMAs'
+    // operand fetch alone saturates -- 8 KB per 64-cycle S step, 6 KB per 32-cycle PV step) | O [192,256)
+    const uint32_t tS = tmem, tP = tmem + 128, tO = tmem + 192;
 
     if (warp >= 8) {
         if (warp == 8 && lane == 0) {
             const uint32_t sQ = sbase + AttnFwdSmem::kQ;
-            const uint32_t sP = sbase + AttnFwdSmem::kP;
             mbar_expect_tx(q_full, 16384);
             tma_load_2d(sQ, &tmQKV, q_full, h * AT_D, row0);
             const uint32_t sK = sbase + AttnFwdSmem::kK0;
@@ -157,11 +158,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                         issue_s();                                       // S_{j+1} ahead of PV_j
                     }
                     {
-                        const uint32_t p_lo = desc_lo(sP, 1), v_lo = desc_lo(sV, 512);
+                        const uint32_t v_lo = desc_lo(sV, 512);
 #pragma unroll
-                        for (int k8 = 0; k8 < AT_BN / 16; ++k8)
-                            umma_bf16(tO, desc_make(p_lo + (k8 >> 2) * 1024 + (k8 & 3) * 2, kHi), desc_make(v_lo + k8 * 128, kHi), idO,
-                                      (uint32_t)((j | k8) != 0));     // accumulates across key tiles
+                        for (int k8 = 0; k8 < AT_BN / 16; ++k8)   // 16 keys = 8 columns of P per step
+                            umma_bf16_ts(tO, tP + k8 * 8, desc_make(v_lo + k8 * 128, kHi), idO,
+                                         (uint32_t)((j | k8) != 0));     // accumulates across key tiles
                     }
                     umma_commit(o_full);
                     umma_commit(v_empty0 + 8 * s);
@@ -203,11 +204,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                 tc_fence_after();
                 // O_j = P V_j : A = P K-major (two 64-key blocks 16 KB apart), B = V MN-major (16 keys = 2048 B per step)
                 {
-                    const uint32_t p_lo = desc_lo(sP, 1), v_lo = desc_lo(sV, 512);
+                    const uint32_t v_lo = desc_lo(sV, 512);
 #pragma unroll
                     for (int k8 = 0; k8 < AT_BN / 16; ++k8)
-                        umma_bf16(tO, desc_make(p_lo + (k8 >> 2) * 1024 + (k8 & 3) * 2, kHi), desc_make(v_lo + k8 * 128, kHi), idO,
-                                  (uint32_t)(k8 != 0));
+                        umma_bf16_ts(tO, tP + k8 * 8, desc_make(v_lo + k8 * 128, kHi), idO, (uint32_t)(k8 != 0));
                 }
                 umma_commit(o_full);
                 umma_commit(v_empty0 + 8 * s);
@@ -227,7 +227,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
 #pragma unroll
         for (int d = 0; d < 32; ++d) o[d] = 0.f;
         float m = -INFINITY, l = 0.f;
-        uint8_t* blk = smem + AttnFwdSmem::kP + half * 16384;   // this half's 64-key block of P
+        const uint32_t tPmine = tP + lane_addr + half * 32;      // this thread's 64 probabilities = 32 packed columns
         int* redo_flag = reinterpret_cast<int*>(sum_s + 256);   // 3 rotating CTA-wide flags (slack after the row sums)
         if (threadIdx.x < 3) redo_flag[threadIdx.x] = 0;
         softmax_pair_sync();
@@ -283,16 +283,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                         mbar_wait(o_full, (uint32_t)((j - 1) & 1));
                         tc_fence_after();
                     }
-#pragma unroll
-                    for (int q4 = 0; q4 < 4; ++q4)
-                        *reinterpret_cast<uint4*>(blk + sw128_off(r, c * 32 + q4 * 8)) =
-                            make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
+                    tmem_st_32x16(tPmine + c * 16, packed);
                 }
+                tmem_st_wait();
                 if (fmaf(mt, scale_log2e, neg_m) > kLazyTau) redo_flag[j % 3] = 1;
                 softmax_pair_sync();
                 if (redo_flag[j % 3] == 0) {
                     tc_fence_before();
-                    fence_async_smem();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(p_ready);
                     l += ls;
@@ -386,13 +383,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __r
                         packed[k >> 1] = pack_bf16x2(pa, pb);
                     }
                 }
-#pragma unroll
-                for (int q4 = 0; q4 < 4; ++q4)
-                    *reinterpret_cast<uint4*>(blk + sw128_off(r, c * 32 + q4 * 8)) =
-                        make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
+                tmem_st_32x16(tPmine + c * 16, packed);
             }
+            tmem_st_wait();
             tc_fence_before();
-            fence_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(p_ready);
             l = (LAZY && j == 0) ? ls : l * corr + ls;
@@ -489,6 +483,7 @@ struct AttnBwdSmem {
 // dQ is double buffered so the reduction of tile it-1 runs under the MMAs of tile it.
 __global__ void __launch_bounds__(576, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                   const __grid_constant__ CUtensorMap tmDQ,
                    const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
                    __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
@@ -511,6 +506,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     if (threadIdx.x == 512) {
         tma_prefetch_desc(&tmQKV);
         tma_prefetch_desc(&tmDO);
+        tma_prefetch_desc(&tmDQ);
         mbar_init(kv_full, 1);
         mbar_init(qg_full0, 1); mbar_init(qg_full0 + 8, 1);
         mbar_init(qg_empty0, 1); mbar_init(qg_empty0 + 8, 1);
@@ -581,6 +577,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 const uint32_t tDQb = tDQ + (uint32_t)(s * 64);
                 mbar_wait(pds_ready, (uint32_t)(it & 1));     // P, dS of this tile are in smem; S/dP TMEM is free again
                 tc_fence_after();
+                // S, dP of the NEXT query tile go first: they only need the S/dP columns the softmax-gradient threads have
+                // just finished reading, and they are what those threads wait for. Issued after dV/dK/dQ (as this loop
+                // first did) the 24 + 8 MMA issues (~65 cycles each) sat between two softmax-gradient passes: 4,600 cycles
+                // per tile, of which the tensor pipe was busy 1,280 (clock64 timeline, round 2). Now the pass over tile
+                // it+1 (~1,900 cycles of exponentials) runs under dV, dK, dQ of tile it.
+                if (it + 1 < n_it) issue_s_dp(it + 1);
 #pragma unroll
                 for (int k8 = 0; k8 < 8; ++k8)   // dV += P^T dO   (M = keys, K = queries; both operands MN-major)
                     umma_bf16(tDV, desc_make(pm_lo + k8 * 128, kHi), desc_make(gm_lo + k8 * 128, kHi), id_mm64,
@@ -595,7 +597,6 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                               id_km64, (uint32_t)(k8 != 0));
                 umma_commit(dq_full);
                 umma_commit(qg_empty0 + 8 * s);
-                if (it + 1 < n_it) issue_s_dp(it + 1);
             }
         }
         __syncwarp();
@@ -612,26 +613,31 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         float lse_next = 0.f, dl_next = 0.f;
         if (jt * AT_BM + r < Tn) { lse_next = lse[stat0 + jt * AT_BM + r]; dl_next = delta[stat0 + jt * AT_BM + r]; }
 
-        // dQ of query tile `t` (TMEM buffer t & 1): 16 columns per thread -> staging -> row-coalesced red.add
+        // dQ of query tile `t` (TMEM buffer t & 1): this warp's [32 rows][16 columns] piece goes to shared memory and from
+        // there into the fp32 accumulator with ONE bulk tensor reduce-add (cp.reduce.async.bulk.tensor ... .add): the TMA
+        // unit performs the 512 atomic adds. Issued per lane as red.global.add.v4 they cost every softmax-gradient warp
+        // ~2,300 cycles per tile (clock64 timeline) -- half of the tile's critical path once S, dP were issued early.
+        // Rows past the sequence end carry dS = 0, so a piece that straddles into the next sequence adds zeros there.
         auto reduce_dq = [&](int t) {
             uint32_t v[16];
             __syncwarp();
             tmem_ld_32x16(tDQ + (uint32_t)((t & 1) * 64) + lane_addr + part * 16, v);
             tmem_ld_wait();
-#pragma unroll
-            for (int k = 0; k < 16; ++k) stg[lane * 17 + k] = __uint_as_float(v[k]);
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // staging is free again
             __syncwarp();
-            const int q0 = (jt + t) * AT_BM + qd * 32;       // first query row of this warp's 32
+            float4* row = reinterpret_cast<float4*>(stg + lane * 16);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int rr = 8 * k + (lane >> 2), cc = (lane & 3) * 4;
-                if (q0 + rr < Tn) {
-                    const float* d = stg + rr * 17 + cc;
-                    float* o = dq_accum + ((size_t)(b * Tn) + q0 + rr) * C + h * AT_D + part * 16 + cc;
-                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o), "f"(d[0]), "f"(d[1]), "f"(d[2]),
-                                 "f"(d[3])
-                                 : "memory");
-                }
+            for (int k = 0; k < 4; ++k)
+                row[k] = make_float4(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]), __uint_as_float(v[4 * k + 2]),
+                                     __uint_as_float(v[4 * k + 3]));
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                const int c0 = h * AT_D + part * 16;
+                const int r0 = b * Tn + (jt + t) * AT_BM + qd * 32;
+                asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];"
+                             ::"l"(&tmDQ), "r"(c0), "r"(r0), "r"(smem_u32(stg)) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
             __syncwarp();
             tc_fence_before();
@@ -648,8 +654,6 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             const bool diag = (it == 0);
             const bool edge = diag || ((qt + 1) * AT_BM > Tn);
             const int key0 = jt * AT_BN + part * 32;
-            // the MMAs of the previous tile must be done with P/dS (and its dQ is complete) before they are overwritten
-            if (it > 0) { mbar_wait(dq_full, (uint32_t)((it - 1) & 1)); }
             mbar_wait(sdp_full, (uint32_t)(it & 1));
             tc_fence_after();
             {
@@ -684,6 +688,9 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                         dd[k >> 1] = pack_bf16x2(d0, d1);
                     }
                 }
+                // dV, dK, dQ of the previous tile (issued after this tile's S, dP) read the P / dS buffers: they must have
+                // retired before the buffers are overwritten -- normally they have, a whole pass of exponentials later
+                if (it > 0) { mbar_wait(dq_full, (uint32_t)((it - 1) & 1)); tc_fence_after(); }
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4) {
                     const uint32_t off = sw128_off(r, (part & 1) * 32 + q4 * 8);
@@ -700,6 +707,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         mbar_wait(dq_full, (uint32_t)((n_it - 1) & 1));
         tc_fence_after();
         reduce_dq(n_it - 1);
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // the adds have landed before the CTA exits
         // dV, dK of this key tile: lane = key row, 16 columns per thread
         const int key = jt * AT_BN + r;
         const bool key_ok = key < Tn;
@@ -756,6 +764,26 @@ static int encode_rows_bf16(CUtensorMap* tm, const void* ptr, uint64_t cols, uin
                                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("attention: cuTensorMapEncodeTiled failed (%d)", (int)r); return PENROZ_ERR_CUDA; }
+    return PENROZ_OK;
+}
+
+// fp32 [rows, cols] accumulator, box {16 columns, 32 rows}, no swizzle: the target of the dQ bulk reduce-add
+static int encode_dq_f32(CUtensorMap* tm, const void* ptr, uint64_t cols, uint64_t rows) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || !sym) {
+        set_error("cuTensorMapEncodeTiled entry point unavailable");
+        return PENROZ_ERR_CUDA;
+    }
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * 4};
+    cuuint32_t box[2] = {16, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = ((EncodeTiledFnA)sym)(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides, box,
+                                       estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("attention: cuTensorMapEncodeTiled (dQ) failed (%d)", (int)r); return PENROZ_ERR_CUDA; }
     return PENROZ_OK;
 }
 
@@ -817,6 +845,9 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     if (rc) return rc;
     rc = encode_rows_bf16(&tmG, dout, (uint64_t)C, rows, 128);
     if (rc) return rc;
+    CUtensorMap tmDQ;
+    rc = encode_dq_f32(&tmDQ, dq_acc, (uint64_t)C, rows);
+    if (rc) return rc;
     static std::atomic<int> configured{0};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -831,7 +862,7 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     attn_bwd_delta_kernel<<<(unsigned)((pairs * 8 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
-    attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
+    attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, tmDQ, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
     size_t n4 = rows * C / 4;
     size_t g = (n4 + 255) / 256;
     size_t cap = (size_t)num_sms() * 16;
