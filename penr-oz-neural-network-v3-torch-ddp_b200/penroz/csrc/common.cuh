@@ -231,6 +231,13 @@ __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const void* tmap,
         : "memory");
 }
 
+// contiguous global -> shared bulk copy (16-byte aligned, size a multiple of 16), completing on an mbarrier
+__device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tmem_alloc(uint32_t smem_result, uint32_t ncols) {

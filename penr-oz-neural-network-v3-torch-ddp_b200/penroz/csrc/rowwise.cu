@@ -8,6 +8,8 @@
 //   ResidualConnection                        neural_net_layers.py:130-135
 // All of them are HBM-bound: one warp per row, 16-byte vector accesses, warp-shuffle reductions.
 #include "common.cuh"
+#include <stdlib.h>
+#include <string.h>
 
 namespace penroz {
 
@@ -361,25 +363,176 @@ layernorm_bwd_cols_kernel(const TG* __restrict__ dy, const TX* __restrict__ x, c
     }
 }
 
-// out_q[c] += sum_blocks scratch[b][q][c]   (fixed summation order: deterministic). 32 columns x 8 partial-sum
-// lanes per CTA, so the ~300 per-block partials are read by 8 threads per column instead of one.
+// One-pass form. The CTA spans the row (thread t owns float4 columns t, t + blockDim, ...), so a thread carries
+// 12 VPT column accumulators instead of the 72 of the row-per-warp kernel above, and dy, x and the residual gradient
+// are read once (the two-kernel form reads dy and x twice and the written gradient back: 24 bytes per element against
+// the 16 the op needs). What keeps HBM busy is not registers but shared memory: R consecutive rows of dy, x and add
+// are three contiguous ranges, so one thread fetches them with bulk copies into a ring of S stages (about 100 KB per
+// CTA, two CTAs per SM) while the others work on an earlier stage. The two row sums cross the warps through a
+// double-buffered shared array: one __syncthreads per R rows, after which the stage consumed before this one is
+// refilled. scratch[block][q][c] as above.
+template <typename TG, int VPT, int R>
 __global__ void __launch_bounds__(256)
+layernorm_bwd_staged_kernel(const TG* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ gamma,
+                            const float* __restrict__ mean, const float* __restrict__ rstd,
+                            const float* __restrict__ add, float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16,
+                            float* __restrict__ scratch, int rows, int C, int S, int want_dcol) {
+    extern __shared__ __align__(128) unsigned char ln_smem[];
+    __shared__ __align__(16) float red[2][R][2][8];
+    __shared__ __align__(8) unsigned long long full_bar[8];
+    const int nv = C >> 2;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t dy_bytes = (uint32_t)R * C * sizeof(TG), x_bytes = (uint32_t)R * C * sizeof(float);
+    const uint32_t x_off = (dy_bytes + 127u) & ~127u, add_off = x_off + ((x_bytes + 127u) & ~127u);
+    const uint32_t stage_bytes = add_off + ((x_bytes + 127u) & ~127u);
+    const int nchunks = (rows + R - 1) / R;
+    const int mine = ((int)blockIdx.x < nchunks) ? (nchunks - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    auto fill = [&](int i) {     // chunk i of this CTA into stage i % S (one thread)
+        const int row0 = ((int)blockIdx.x + i * (int)gridDim.x) * R;
+        const int nr = min(R, rows - row0);
+        const uint32_t bar = smem_u32(&full_bar[i % S]);
+        const uint32_t base = smem_u32(ln_smem) + (uint32_t)(i % S) * stage_bytes;
+        const uint32_t nb_dy = (uint32_t)nr * C * sizeof(TG), nb_x = (uint32_t)nr * C * sizeof(float);
+        mbar_expect_tx(bar, nb_dy + nb_x + (add ? nb_x : 0u));
+        bulk_load_1d(base, dy + (size_t)row0 * C, nb_dy, bar);
+        bulk_load_1d(base + x_off, x + (size_t)row0 * C, nb_x, bar);
+        if (add) bulk_load_1d(base + add_off, add + (size_t)row0 * C, nb_x, bar);
+    };
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) mbar_init(smem_u32(&full_bar[s]), 1);
+        mbar_fence_init();
+        for (int i = 0; i < S && i < mine; ++i) fill(i);
+    }
+    for (int i = tid; i < 2 * R * 2 * 8; i += blockDim.x) (&red[0][0][0][0])[i] = 0.f;   // absent warps add zero
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 gam[VPT], ag[VPT], ab[VPT], ac[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = tid + k * blockDim.x;
+        gam[k] = (v < nv) ? load4(gamma + 4 * v) : zero4;
+        ag[k] = zero4; ab[k] = zero4; ac[k] = zero4;
+    }
+    const float invC = 1.f / (float)C;
+    float mu_n[R], rs_n[R];   // row statistics of the next chunk, fetched one iteration ahead
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int row = (int)blockIdx.x * R + r;
+        mu_n[r] = (row < rows) ? mean[row] : 0.f;
+        rs_n[r] = (row < rows) ? rstd[row] : 0.f;
+    }
+    __syncthreads();   // barriers initialised, red zeroed
+    for (int i = 0; i < mine; ++i) {
+        const int row0 = ((int)blockIdx.x + i * (int)gridDim.x) * R;
+        const int nr = min(R, rows - row0);
+        const int buf = i & 1;
+        float mu[R], rs[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            mu[r] = mu_n[r]; rs[r] = rs_n[r];
+            const int row = row0 + (int)gridDim.x * R + r;
+            mu_n[r] = (row < rows) ? mean[row] : 0.f;
+            rs_n[r] = (row < rows) ? rstd[row] : 0.f;
+        }
+        const unsigned char* st = ln_smem + (size_t)(i % S) * stage_bytes;
+        const TG* sdy = reinterpret_cast<const TG*>(st);
+        const float* sx = reinterpret_cast<const float*>(st + x_off);
+        const float* sadd = reinterpret_cast<const float*>(st + add_off);
+        mbar_wait(smem_u32(&full_bar[i % S]), (uint32_t)((i / S) & 1));
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            float s1 = 0.f, s2 = 0.f;
+            if (r < nr) {
+#pragma unroll
+                for (int k = 0; k < VPT; ++k) {
+                    const int v = tid + k * blockDim.x;
+                    if (v < nv) {
+                        const float4 d = load4(sdy + (size_t)r * C + 4 * v), xv = load4(sx + (size_t)r * C + 4 * v);
+                        const float4 g = gam[k];
+                        const float4 h = make_float4((xv.x - mu[r]) * rs[r], (xv.y - mu[r]) * rs[r],
+                                                     (xv.z - mu[r]) * rs[r], (xv.w - mu[r]) * rs[r]);
+                        const float a = d.x * g.x, b = d.y * g.y, c = d.z * g.z, e = d.w * g.w;
+                        s1 += (a + b) + (c + e);
+                        s2 += (a * h.x + b * h.y) + (c * h.z + e * h.w);
+                        ag[k].x += d.x * h.x; ag[k].y += d.y * h.y; ag[k].z += d.z * h.z; ag[k].w += d.w * h.w;
+                        ab[k].x += d.x; ab[k].y += d.y; ab[k].z += d.z; ab[k].w += d.w;
+                    }
+                }
+            }
+            s1 = warp_sum(s1);
+            s2 = warp_sum(s2);
+            if (lane == 0) { red[buf][r][0][warp] = s1; red[buf][r][1][warp] = s2; }
+        }
+        __syncthreads();
+        // every thread is past its reads of the stage consumed in the previous iteration: refill it
+        if (tid == 0 && i >= 1 && i - 1 + S < mine) fill(i - 1 + S);
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (r < nr) {
+                const float4 a0 = *reinterpret_cast<const float4*>(&red[buf][r][0][0]);
+                const float4 a1 = *reinterpret_cast<const float4*>(&red[buf][r][0][4]);
+                const float4 b0 = *reinterpret_cast<const float4*>(&red[buf][r][1][0]);
+                const float4 b1 = *reinterpret_cast<const float4*>(&red[buf][r][1][4]);
+                const float s1 = (((a0.x + a0.y) + (a0.z + a0.w)) + ((a1.x + a1.y) + (a1.z + a1.w))) * invC;
+                const float s2 = (((b0.x + b0.y) + (b0.z + b0.w)) + ((b1.x + b1.y) + (b1.z + b1.w))) * invC;
+#pragma unroll
+                for (int k = 0; k < VPT; ++k) {
+                    const int v = tid + k * blockDim.x;
+                    if (v < nv) {
+                        const float4 d = load4(sdy + (size_t)r * C + 4 * v), xv = load4(sx + (size_t)r * C + 4 * v);
+                        const float4 ad = add ? load4(sadd + (size_t)r * C + 4 * v) : zero4;
+                        const float4 g = gam[k];
+                        float4 o;
+                        o.x = rs[r] * (d.x * g.x - s1 - (xv.x - mu[r]) * rs[r] * s2) + ad.x;
+                        o.y = rs[r] * (d.y * g.y - s1 - (xv.y - mu[r]) * rs[r] * s2) + ad.y;
+                        o.z = rs[r] * (d.z * g.z - s1 - (xv.z - mu[r]) * rs[r] * s2) + ad.z;
+                        o.w = rs[r] * (d.w * g.w - s1 - (xv.w - mu[r]) * rs[r] * s2) + ad.w;
+                        const size_t off = (size_t)(row0 + r) * C + 4 * v;
+                        store4(dx + off, o);
+                        if (dx_bf16) {
+                            store4(dx_bf16 + off, o);
+                            // the bias gradient of the Linear that produced this residual branch sums the gradient
+                            // as that Linear sees it: rounded to bf16 when a bf16 copy is requested
+                            o.x = bf16_round(o.x); o.y = bf16_round(o.y); o.z = bf16_round(o.z); o.w = bf16_round(o.w);
+                        }
+                        ac[k].x += o.x; ac[k].y += o.y; ac[k].z += o.z; ac[k].w += o.w;
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = tid + k * blockDim.x;
+        if (v < nv) {
+            float* s = scratch + (size_t)blockIdx.x * 3 * C + 4 * v;
+            *reinterpret_cast<float4*>(s) = ag[k];
+            *reinterpret_cast<float4*>(s + C) = ab[k];
+            if (want_dcol) *reinterpret_cast<float4*>(s + 2 * (size_t)C) = ac[k];
+        }
+    }
+}
+
+// out_q[c] += sum_blocks scratch[b][q][c]   (fixed summation order: deterministic). 32 columns x 32 partial-sum
+// lanes per CTA, so the several hundred per-block partials of a column are a few independent loads per thread.
+__global__ void __launch_bounds__(1024)
 layernorm_bwd_reduce_kernel(const float* __restrict__ scratch, int nblocks, int C, float* __restrict__ dgamma,
                             float* __restrict__ dbeta, float* __restrict__ dcol) {
-    __shared__ float sm[8][33];
+    __shared__ float sm[32][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + tx;
     const int qn = blockIdx.y;
     float* dst = (qn == 0) ? dgamma : (qn == 1) ? dbeta : dcol;
     float s = 0.f;
-    if (dst && c < C)
-        for (int b = ty; b < nblocks; b += 8) s += scratch[((size_t)b * 3 + qn) * C + c];
+    if (dst && c < C) {
+#pragma unroll 8
+        for (int b = ty; b < nblocks; b += 32) s += scratch[((size_t)b * 3 + qn) * C + c];
+    }
     sm[ty][tx] = s;
     __syncthreads();
     if (ty == 0 && dst && c < C) {
         float t = sm[0][tx];
 #pragma unroll
-        for (int k = 1; k < 8; ++k) t += sm[k][tx];
+        for (int k = 1; k < 32; ++k) t += sm[k][tx];
         dst[c] += t;
     }
 }
@@ -618,10 +771,20 @@ extern "C" int penroz_layernorm_fwd(const void* x, const void* gamma, const void
 }
 
 // scratch must hold penroz_layernorm_bwd_scratch_bytes(rows, C) bytes
-static int ln_bwd_grid(int rows) {
+static int ln_bwd_grid_old(int rows) {
     int g = (rows + 7) / 8;
     int cap = 2 * num_sms();
     return g < cap ? g : cap;
+}
+// upper bound of the one-pass kernel's CTAs = per-block partial-sum slots in scratch (at most 4 resident per SM)
+static int ln_bwd_grid(int rows) {
+    int g = (rows + 1) / 2;
+    int cap = 4 * num_sms();
+    return g < 1 ? 1 : (g < cap ? g : cap);
+}
+static bool ln_bwd_two_kernel() {
+    static const bool on = getenv("PENROZ_LN_BWD") && !strcmp(getenv("PENROZ_LN_BWD"), "two-kernel");
+    return on;
 }
 extern "C" size_t penroz_layernorm_bwd_scratch_bytes(int rows, int C) {
     return (size_t)ln_bwd_grid(rows) * 3 * (size_t)C * sizeof(float);
@@ -637,6 +800,59 @@ int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const f
     PENROZ_REQUIRE(scratch != nullptr, "layernorm_bwd: scratch is required");
     const int J = (C + 127) / 128;
     int grid = ln_bwd_grid(rows);
+    // one-pass staged kernel: fp32 x / gamma, rows of 16-byte multiples in every operand, at least two stages
+    {
+        const int nv = C / 4, vpt = nv <= 256 ? 1 : 2;
+        const int threads = (((nv + vpt - 1) / vpt) + 31) / 32 * 32;
+        const size_t esz = dy_dtype == BF16 ? 2 : 4;
+        auto stage_bytes = [&](int R) {
+            const size_t a = ((size_t)R * C * esz + 127) & ~(size_t)127, b = ((size_t)R * C * 4 + 127) & ~(size_t)127;
+            return a + 2 * b;
+        };
+        // measured (32768 x 768 / x 1024, 16384 x 1600): resident warps matter more than ring depth -- 2 rows per
+        // stage, 3 stages, as many CTAs per SM as 200 KB of shared memory hold (4 / 3 / 2): 74 / 91 / 76 us, 5.4-5.9
+        // TB/s of the op's bytes; 4-row stages or deeper rings with fewer CTAs are 10-40 % slower
+        const int R = 2;
+        int S = 3;
+        if ((size_t)S * stage_bytes(R) > 200 * 1024) S = 2;
+        int per_sm = (int)((size_t)200 * 1024 / ((size_t)S * stage_bytes(R) + 1024));
+        per_sm = per_sm > 4 ? 4 : per_sm;
+        const bool ok = !ln_bwd_two_kernel() && x_dtype == F32 && w_dtype == F32 && (dy_dtype == BF16 || dy_dtype == F32) &&
+                        C % 8 == 0 && per_sm >= 1 &&
+                        (((uintptr_t)dy | (uintptr_t)x | (uintptr_t)add) & 15) == 0;
+        if (ok) {
+            const int nchunks = (rows + R - 1) / R;
+            grid = per_sm * num_sms();            // <= ln_bwd_grid's cap, which sizes scratch
+            if (grid > nchunks) grid = nchunks;
+            const size_t smem = (size_t)S * stage_bytes(R);
+            cudaError_t e = cudaSuccess;
+            int dev = 0;
+            cudaGetDevice(&dev);
+#define LN_STAGED(TG, V, RR)                                                                                            \
+            {                                                                                                           \
+                auto k = layernorm_bwd_staged_kernel<TG, V, RR>;                                                        \
+                static std::atomic<int> granted[64];                                                                    \
+                if (!granted[dev & 63].load(std::memory_order_relaxed)) {                                               \
+                    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);               \
+                    if (e == cudaSuccess) granted[dev & 63].store(1, std::memory_order_relaxed);                        \
+                }                                                                                                       \
+                if (e == cudaSuccess)                                                                                   \
+                    k<<<grid, threads, smem, st>>>((const TG*)dy, (const float*)x, (const float*)gamma, mean, rstd,      \
+                                                   (const float*)add, (float*)dx, (__nv_bfloat16*)dx_bf16, scratch, rows, \
+                                                   C, S, dcol != nullptr);                                              \
+            }
+            if (dy_dtype == BF16) { if (vpt == 1) LN_STAGED(__nv_bfloat16, 1, 2) else LN_STAGED(__nv_bfloat16, 2, 2) }
+            else { if (vpt == 1) LN_STAGED(float, 1, 2) else LN_STAGED(float, 2, 2) }
+#undef LN_STAGED
+            if (e != cudaSuccess) { set_error("layernorm_bwd: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
+            dim3 rg((C + 31) / 32, dcol ? 3 : 2);
+            layernorm_bwd_reduce_kernel<<<rg, 1024, 0, st>>>(scratch, grid, C, dgamma, dbeta, dcol);
+            count_launch(2);
+            return check_launch("layernorm_bwd");
+        }
+    }
+    // ---- two-kernel form of round 1: other operand types and alignments, and PENROZ_LN_BWD=two-kernel for A/B
+    grid = ln_bwd_grid_old(rows);
     bool fuse_dcol = dcol != nullptr && J <= 8;
     int rc = -1;
     const bool wide = rows >= 4096;   // enough rows to fill the GPU with the one-row-per-warp kernel
@@ -648,7 +864,7 @@ int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const f
         else if (J <= 4) LN_ROWS_J(TX, TW, TG, 4); else if (J <= 6) LN_ROWS_J(TX, TW, TG, 6); \
         else if (J <= 8) LN_ROWS_J(TX, TW, TG, 8); else if (J <= 13) LN_ROWS_J(TX, TW, TG, 13); \
         else LN_ROWS_J(TX, TW, TG, 16)
-        grid = ln_bwd_grid(rows);        // number of row slices == partial-sum slots in scratch
+        grid = ln_bwd_grid_old(rows);    // number of row slices == partial-sum slots in scratch
         dim3 cg((C + 127) / 128, grid);
         if (x_dtype == F32 && w_dtype == F32 && dy_dtype == BF16) {
             LN_ROWS(float, float, __nv_bfloat16);
@@ -673,7 +889,7 @@ int layernorm_bwd_impl(const void* dy, const void* x, const void* gamma, const f
     }
     if (rc != 0) { set_error("layernorm_bwd: no kernel for C=%d", C); return PENROZ_ERR_ARG; }
     dim3 rg((C + 31) / 32, fuse_dcol ? 3 : 2);
-    layernorm_bwd_reduce_kernel<<<rg, 256, 0, st>>>(scratch, grid, C, dgamma, dbeta, fuse_dcol ? dcol : nullptr);
+    layernorm_bwd_reduce_kernel<<<rg, 1024, 0, st>>>(scratch, grid, C, dgamma, dbeta, fuse_dcol ? dcol : nullptr);
     count_launch(2);
     int e = check_launch("layernorm_bwd");
     if (e) return e;
