@@ -21,6 +21,7 @@
 //     below), so a grid that loses SMs to a concurrent kernel (the gradient all-reduce) slows down in proportion
 //     instead of waiting for its unlucky CTAs.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace penroz {
 
@@ -363,6 +364,211 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&acc)
     }
 }
 
+// ------------------------------------------------------------------ epilogue of the pair kernel: registers ->
+// swizzled shared memory -> bulk tensor store. A thread owns one accumulator row (tcgen05.ld hands TMEM out that way):
+// it packs its 32 columns of the chunk, writes them as 16-byte pieces into a [32 rows][32 columns] box laid out with
+// the TMA swizzle (conflict-free), and one lane hands the box to the TMA unit (cp.async.bulk.tensor store, or
+// cp.reduce ... .add for the accumulating weight-gradient form, which replaces a load-add-store round trip or 1024
+// red.global per chunk). Rows and columns past M / N are clipped by the tensor map. The round-1 epilogue moved every
+// element through an fp32 staging tile twice (33-float stride transpose) to get row-contiguous global accesses: 11
+// instructions per element for a plain bf16 store and 38 with GELU, which made the GELU / GELU' GEMMs epilogue-bound
+// (ncu: 120.8 M warp instructions against 26.5 M for the plain kernel, 201 us against ~125 us of mainloop).
+template <int EPI> struct EpiTraits {
+    static constexpr bool kF32Out = (EPI == EPI_RESID_F32 || EPI == EPI_ACCUM_F32 || EPI == EPI_F32);
+    static constexpr bool kHasAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16);
+    static constexpr bool kAuxF32 = (EPI == EPI_RESID_F32);
+    static constexpr int kBoxBytes = kF32Out ? 4096 : 2048;
+};
+constexpr int kStgPerWarp = 4096;   // one fp32 box, or two bf16 boxes (alternating; out / out2 for GELU)
+
+__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t smem_src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(tmap), "r"(smem_src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t smem_src, int c0, int c1) {
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(tmap), "r"(smem_src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// this thread's row of a bf16 box (32 rows x 64 B, SWIZZLE_64B: 16-byte piece j of row r sits at j ^ ((r >> 1) & 3))
+__device__ __forceinline__ void box_put_bf16(uint32_t box, int lane, const uint32_t (&w)[16]) {
+    const uint32_t row = box + (uint32_t)lane * 64u, x = ((uint32_t)lane >> 1) & 3u;
+#pragma unroll
+    for (uint32_t j = 0; j < 4; ++j) sts128(row + ((j ^ x) << 4), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+}
+// fp32 box (32 rows x 128 B, SWIZZLE_128B: piece j of row r at j ^ (r & 7))
+__device__ __forceinline__ void box_put_f32(uint32_t box, int lane, const float (&a)[32]) {
+    const uint32_t row = box + (uint32_t)lane * 128u, x = (uint32_t)lane & 7u;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; ++j)
+        sts128(row + ((j ^ x) << 4), __float_as_uint(a[4 * j]), __float_as_uint(a[4 * j + 1]), __float_as_uint(a[4 * j + 2]),
+               __float_as_uint(a[4 * j + 3]));
+}
+// hand a filled box to the TMA unit. PENDING = bulk groups of this lane that may still be reading shared memory when
+// the box is written (the other box of an alternating pair).
+template <int PENDING>
+__device__ __forceinline__ void box_begin(int lane) {
+    if (lane == 0) bulk_wait_read<PENDING>();
+    __syncwarp();
+}
+__device__ __forceinline__ void box_send(const void* tmap, uint32_t box, int lane, int col0, int row0, bool reduce) {
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+        if (reduce) tma_reduce_add_2d(tmap, box, col0, row0); else tma_store_2d(tmap, box, col0, row0);
+        bulk_commit();
+    }
+}
+
+// Epilogues with an aux operand: the aux chunk sits in a swizzled box (bulk tensor load), is replaced in place by the
+// result (a thread touches only its own row's bytes) and leaves by a bulk tensor store from the same box.
+//   EPI_RESID_F32  fp32 box (SWIZZLE_128B): box += bf16(acc + bias)
+//   EPI_RESID_BF16 bf16 box (SWIZZLE_64B):  box = bf16(box + bf16(acc + bias))
+//   EPI_DGELU      bf16 box:                box = bf16(bf16(acc) * gelu'(box))
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk_box(const GemmParams& p, const uint32_t (&v)[32], uint32_t box, int lane,
+                                                   int col0) {
+    float acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
+    if (EPI != EPI_DGELU && p.bias != nullptr) {
+        if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(p.bias + col0) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 w = *reinterpret_cast<const uint4*>(p.bias + col0 + 8 * j);
+                const uint32_t bw[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 b = unpack_bf16x2(bw[k]);
+                    acc[8 * j + 2 * k] += b.x; acc[8 * j + 2 * k + 1] += b.y;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
+        }
+    }
+    if (EPI == EPI_RESID_F32) {
+        const uint32_t row = box + (uint32_t)lane * 128u, x = (uint32_t)lane & 7u;
+#pragma unroll
+        for (uint32_t j = 0; j < 8; ++j) {
+            const uint32_t addr = row + ((j ^ x) << 4);
+            float4 a;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(addr) : "memory");
+            sts128(addr, __float_as_uint(a.x + bf16_round(acc[4 * j])), __float_as_uint(a.y + bf16_round(acc[4 * j + 1])),
+                   __float_as_uint(a.z + bf16_round(acc[4 * j + 2])), __float_as_uint(a.w + bf16_round(acc[4 * j + 3])));
+        }
+    } else {
+        const uint32_t row = box + (uint32_t)lane * 64u, x = ((uint32_t)lane >> 1) & 3u;
+        uint32_t h[16];
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j)
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(h[4 * j]), "=r"(h[4 * j + 1]), "=r"(h[4 * j + 2]), "=r"(h[4 * j + 3])
+                         : "r"(row + ((j ^ x) << 4)) : "memory");
+        uint32_t w[16];
+        if (EPI == EPI_RESID_BF16) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 a = unpack_bf16x2(h[i]);
+                w[i] = pack_bf16x2(a.x + bf16_round(acc[2 * i]), a.y + bf16_round(acc[2 * i + 1]));
+            }
+        } else if (p.gelu_tanh) {   // warp-uniform choice outside the element loop: straight-line code per element
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 a = unpack_bf16x2(h[i]);
+                w[i] = pack_bf16x2(bf16_round(acc[2 * i]) * gelu_tanh_grad_fast(a.x), bf16_round(acc[2 * i + 1]) * gelu_tanh_grad_fast(a.y));
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 a = unpack_bf16x2(h[i]);
+                float lo, hi;
+                gelu_erf_grad_times_fast2(a.x, a.y, bf16_round(acc[2 * i]), bf16_round(acc[2 * i + 1]), lo, hi);
+                w[i] = pack_bf16x2(lo, hi);
+            }
+        }
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) sts128(row + ((j ^ x) << 4), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+    }
+}
+
+// Epilogues without an aux operand (EPI_BF16, EPI_GELU, EPI_F32, EPI_ACCUM_F32): registers -> box -> store
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk_ts(const GemmParams& p, const void* tmO, const void* tmO2,
+                                                  const uint32_t (&v)[32], uint32_t stg, int& nbox, int lane, int row0,
+                                                  int col0) {
+    using T = EpiTraits<EPI>;
+    float acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
+    // ---- bias (same 64 B for every lane: broadcast loads)
+    if (EPI != EPI_ACCUM_F32 && p.bias != nullptr) {
+        if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(p.bias + col0) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 w = *reinterpret_cast<const uint4*>(p.bias + col0 + 8 * j);
+                const uint32_t bw[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 b = unpack_bf16x2(bw[k]);
+                    f2_unpack(f2_add(f2_pack(acc[8 * j + 2 * k], acc[8 * j + 2 * k + 1]), f2_pack(b.x, b.y)), acc[8 * j + 2 * k],
+                              acc[8 * j + 2 * k + 1]);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N) acc[i] += __bfloat162float(p.bias[col0 + i]);
+        }
+    }
+    if constexpr (T::kF32Out) {
+        box_begin<0>(lane);
+        box_put_f32(stg, lane, acc);
+        box_send(tmO, stg, lane, col0, row0, EPI == EPI_ACCUM_F32 && (p.splits > 1 || p.beta));
+    } else {
+    uint32_t w[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = pack_bf16x2(acc[2 * i], acc[2 * i + 1]);
+    const uint32_t box = stg + (uint32_t)(nbox & 1) * 2048u;
+    box_begin<1>(lane);
+    box_put_bf16(box, lane, w);
+    box_send(tmO, box, lane, col0, row0, false);
+    ++nbox;
+    if (EPI == EPI_GELU) {
+        // the activation of the rounded pre-activation, through the other box
+        if (p.gelu_tanh) {   // warp-uniform choice outside the element loop: straight-line code per element
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 r = unpack_bf16x2(w[i]);
+                w[i] = pack_bf16x2(gelu_tanh_fast(r.x), gelu_tanh_fast(r.y));
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 r = unpack_bf16x2(w[i]);
+                float lo, hi;
+                gelu_erf_fast2(r.x, r.y, lo, hi);
+                w[i] = pack_bf16x2(lo, hi);
+            }
+        }
+        const uint32_t box2 = stg + (uint32_t)(nbox & 1) * 2048u;
+        box_begin<1>(lane);
+        box_put_bf16(box2, lane, w);
+        box_send(tmO2, box2, lane, col0, row0, false);
+        ++nbox;
+    }
+    }
+}
+
 template <int BN> struct GemmCfg {
     static constexpr int kABytes = BM * BK * 2;
     static constexpr int kBBytes = BN * BK * 2;
@@ -592,26 +798,34 @@ gemm_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // traffic per flop through L2 drops by a third and the smem ring gets 6 stages deep. The even CTA issues every
 // tcgen05.mma.cta_group::2 (M = 256) and owns the full / tmem-empty barriers; completion of MMAs is multicast to both
 // CTAs' empty / tmem-full barriers. Epilogue code is shared with the single-CTA kernel.
-// EW = epilogue warps per CTA: 8 for light epilogues (6 smem stages), 16 for the activation-math epilogues (GELU,
-// GELU'), whose instruction count per tile exceeds the mainloop's duration with 8 warps (4 stages leave room for the
-// 16 staging tiles).
-template <int EW> struct GemmCfg2 {
+// EW = epilogue warps per CTA. Measured with the register -> TMA-store epilogue: 16 warps (5 stages) are no faster
+// than 8 (6 stages) for any epilogue, so 8 it is.
+// The fp32 residual epilogue keeps two 4 KB boxes per warp: the residual chunk arrives in one by a bulk tensor load,
+// is updated in place and leaves from the same box by a bulk tensor store, while the other box's load is in flight
+// (row-owner register loads of a [32][32] fp32 chunk are 32 cache lines per instruction, and went through the LSU tag
+// stage at 6 us per tile). That takes one stage of the operand ring.
+template <int EW, int EPI> struct GemmCfg2 {
     static constexpr int BN = 256;
     static constexpr int kABytes = BM * BK * 2;            // 128 rows of A
     static constexpr int kBBytes = (BN / 2) * BK * 2;      // this CTA's half of B
     static constexpr int kStageBytes = kABytes + kBBytes;  // 32 KB
-    static constexpr int kStages = (EW == 16) ? 4 : 6;
+    static constexpr bool kAuxBoxes = EpiTraits<EPI>::kHasAux;
+    static constexpr int kBoxBytes = EpiTraits<EPI>::kBoxBytes;
+    static constexpr int kStgWarp = (EPI == EPI_RESID_F32) ? 2 * kStgPerWarp : kStgPerWarp;   // two boxes either way
+    static constexpr int kStages = (EPI == EPI_RESID_F32) ? 5 : 6;
     static constexpr int kTmemCols = 2 * BN;
-    static constexpr int kStagingBytes = EW * 32 * 33 * 4;
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kStagingBytes;
+    static constexpr int kStagingBytes = EW * kStgWarp;    // TMA boxes, 1024-byte aligned behind the barriers
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 1024 /*barriers*/ + kStagingBytes;
     static constexpr int kThreads = (4 + EW) * 32;
+    static_assert(kSmemBytes <= 232448, "pair kernel exceeds the shared memory of an SM");
 };
 
 template <int EPI, int EW>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((4 + EW) * 32, 1)
 gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2,
                      const GemmParams p) {
-    using Cfg = GemmCfg2<EW>;
+    using Cfg = GemmCfg2<EW, EPI>;
     constexpr int BN = Cfg::BN;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
@@ -636,6 +850,8 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         if (leader) first_unit = atomicAdd(&g_feed[p.feed_slot][0], 1u);
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmO);
+        if (EPI == EPI_GELU) tma_prefetch_desc(&tmO2);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < Cfg::kStages; ++s) {
@@ -646,6 +862,8 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             mbar_init(tfull_bar(s), 1);    // one multicast commit
             mbar_init(tempty_bar(s), 2 * EW);  // every epilogue warp of both CTAs (only the leader's copy is used)
         }
+        if (Cfg::kAuxBoxes)
+            for (int w = 0; w < 2 * EW; ++w) mbar_init(bar_base + 512u + 8u * w, 1);
         for (int s = 0; s < kFeedSlots; ++s) {
             mbar_init(feed_full(feed, s), 1);
             // readers: the leader's MMA warp, the odd CTA's producer, every epilogue warp of both CTAs
@@ -771,55 +989,89 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------------ epilogue (both CTAs, own 128 accumulator rows)
+        // TMEM lane quarter = warp % 4 (hardware rule), column slice = (warp - 4) / 4. The accumulator buffer is handed
+        // back to the MMA warp as soon as this warp's last chunk sits in registers, before its math and stores.
         const int q = warp & 3;
-        const int half = (warp - 4) >> 2;
-        constexpr int kChunks = BN / 32 / (EW / 4);   // EW / 4 column slices
-        constexpr bool kPrefetch = (EW == 8);         // with 16 warps the extra registers cost more than the latency
-        float* stg = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256) + (warp - 4) * (32 * 33);
-        int as = 0;
-        uint32_t aph = 0;
+        const int slice = (warp - 4) >> 2;
+        constexpr int kChunks = BN / 32 / (EW / 4);
+        const uint32_t stg = smem_base + Cfg::kStages * Cfg::kStageBytes + 1024 + (uint32_t)(warp - 4) * Cfg::kStgWarp;
+        const uint32_t aux_bar = bar_base + 512u + 16u * (uint32_t)(warp - 4);   // two mbarriers per epilogue warp
+        int as = 0, nbox = 0;
+        uint32_t aph = 0, aux_ph = 0;
         FeedCursor<true> cur(feed, !leader);
         for (int u = cur.next(lane); u >= 0; u = cur.next(lane)) {
             const int tile = u % (p.tiles_m * p.tiles_n);
             const int m0 = (tile / p.tiles_n) * (2 * BM) + (int)rank * BM;
             const int n0 = (tile % p.tiles_n) * BN;
             const int row0 = m0 + q * 32;
-            constexpr bool kHasAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16);
-            uint4 pre[8];
-            bool pre_valid = false;
-            {
-                const int c0 = n0 + half * kChunks * 32;
-                if (kPrefetch && kHasAux && row0 < p.M && c0 < p.N && chunk_is_fast<EPI>(p, c0)) {
-                    aux_issue<EPI>(p, pre, lane, row0, c0);
-                    pre_valid = true;
+            const int c_first = n0 + slice * kChunks * 32;
+            if constexpr (Cfg::kAuxBoxes) {
+                // residual chunks cc and cc + 1 go into boxes 0 and 1 now; chunk cc + 2 follows into box cc & 1 once the
+                // store of chunk cc has read it
+                auto load_box = [&](int cc) {
+                    const uint32_t bar = aux_bar + 8u * (cc & 1);
+                    mbar_expect_tx(bar, (uint32_t)Cfg::kBoxBytes);
+                    tma_load_2d(stg + (uint32_t)((cc & 1) * Cfg::kBoxBytes), &tmO2, bar, c_first + cc * 32, row0);
+                };
+                const bool live = row0 < p.M;
+                if (lane == 0 && live) {
+                    if (c_first < p.N) load_box(0);
+                    if (c_first + 32 < p.N) load_box(1);
                 }
-            }
+#pragma unroll 1
+                for (int cc = 0; cc < kChunks; ++cc) {
+                    const int col0 = c_first + cc * 32;
+                    uint32_t v[32];
+                    if (cc == 0) { mbar_wait(tfull_bar(as), aph); tc_fence_after(); }
+                    __syncwarp();
+                    tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + (col0 - n0)), v);
+                    tmem_ld_wait();
+                    if (cc == kChunks - 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_on_leader(tempty_bar(as));
+                    }
+                    if (col0 >= p.N || !live) continue;   // warp-uniform
+                    const uint32_t box = stg + (uint32_t)((cc & 1) * Cfg::kBoxBytes);
+                    mbar_wait(aux_bar + 8u * (cc & 1), (aux_ph >> (cc & 1)) & 1u);
+                    aux_ph ^= 1u << (cc & 1);
+                    epilogue_chunk_box<EPI>(p, v, box, lane, col0);
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&tmO, box, col0, row0);
+                        bulk_commit();
+                        if (cc + 2 < kChunks && col0 + 64 < p.N) {
+                            bulk_wait_read<0>();
+                            load_box(cc + 2);
+                        }
+                    }
+                }
+                if (lane == 0) bulk_wait_read<0>();   // both boxes are free for the next tile's loads
+                __syncwarp();
+            } else {
             mbar_wait(tfull_bar(as), aph);
             tc_fence_after();
 #pragma unroll 1
             for (int cc = 0; cc < kChunks; ++cc) {
-                const int c = half * kChunks + cc;
+                const int col0 = c_first + cc * 32;
                 uint32_t v[32];
                 __syncwarp();
-                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + (col0 - n0)), v);
                 tmem_ld_wait();
-                const int col0 = n0 + c * 32;
-                if (col0 >= p.N || row0 >= p.M) continue;
-                const bool full = (col0 + 32 <= p.N);
-                float acc[32];
-#pragma unroll
-                for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
-                int next_col0 = -1;
-                if (kPrefetch && kHasAux && cc + 1 < kChunks && col0 + 32 < p.N && chunk_is_fast<EPI>(p, col0 + 32)) next_col0 = col0 + 32;
-                epilogue_chunk<EPI>(p, acc, stg, lane, row0, col0, full, pre, pre_valid, next_col0);
-                pre_valid = (next_col0 >= 0);
+                if (cc == kChunks - 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_on_leader(tempty_bar(as));
+                }
+                if (col0 >= p.N || row0 >= p.M) continue;   // warp-uniform
+                epilogue_chunk_ts<EPI>(p, &tmO, &tmO2, v, stg, nbox, lane, row0, col0);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_on_leader(tempty_bar(as));
+            }
             as ^= 1;
             if (as == 0) aph ^= 1u;
         }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores have left shared memory
     }
 
     tc_fence_before();
@@ -864,6 +1116,27 @@ static int encode_bf16_2d(CUtensorMap* tm, const void* ptr, uint64_t inner, uint
     return PENROZ_OK;
 }
 
+// output matrix of the pair kernel: box {32 columns, 32 rows}; bf16 rows of 64 B (SWIZZLE_64B), fp32 rows of 128 B
+// (SWIZZLE_128B) -- the layouts box_put_bf16 / box_put_f32 write
+static int encode_out_2d(CUtensorMap* tm, const void* ptr, bool f32, uint64_t cols, uint64_t rows, uint64_t ld) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) { set_error("cuTensorMapEncodeTiled entry point unavailable"); return PENROZ_ERR_CUDA; }
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * (f32 ? 4u : 2u)};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr),
+                    dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    f32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (output) failed (%d): ptr=%p cols=%llu rows=%llu ld=%llu", (int)r, ptr,
+                  (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)ld);
+        return PENROZ_ERR_CUDA;
+    }
+    return PENROZ_OK;
+}
+
 template <int BN, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
@@ -881,9 +1154,12 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     return check_launch("gemm_bf16_tc");
 }
 
+struct OutMaps { CUtensorMap o, o2; };
+
 template <int EPI, int EW>
-static int launch_gemm2_ew(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
-    using Cfg2 = GemmCfg2<EW>;
+static int launch_gemm2_ew(const CUtensorMap& tmA, const CUtensorMap& tmB, const OutMaps& om, const GemmParams& p, int grid,
+                           cudaStream_t st) {
+    using Cfg2 = GemmCfg2<EW, EPI>;
     auto kern = gemm_bf16_tc2_kernel<EPI, EW>;
     static std::atomic<int> configured{0};
     int dev = 0;
@@ -893,27 +1169,25 @@ static int launch_gemm2_ew(const CUtensorMap& tmA, const CUtensorMap& tmB, const
         if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
         configured.fetch_or(1 << dev);
     }
-    kern<<<grid, Cfg2::kThreads, Cfg2::kSmemBytes, st>>>(tmA, tmB, p);
+    kern<<<grid, Cfg2::kThreads, Cfg2::kSmemBytes, st>>>(tmA, tmB, om.o, om.o2, p);
     count_launch();
     return check_launch("gemm_bf16_tc2");
 }
-// 16 epilogue warps where the epilogue, not the mainloop, sets the tile time: the activation-math epilogues always,
-// the fp32 residual epilogue (256 KB of global traffic per tile) when the reduction is short
 template <int EPI>
-static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
-    if (EPI == EPI_GELU || EPI == EPI_DGELU) return launch_gemm2_ew<EPI, 16>(tmA, tmB, p, grid, st);
-    if (EPI == EPI_RESID_F32 && p.K <= 1024) return launch_gemm2_ew<EPI_RESID_F32, 16>(tmA, tmB, p, grid, st);
-    return launch_gemm2_ew<EPI, 8>(tmA, tmB, p, grid, st);
+static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const OutMaps& om, const GemmParams& p, int grid,
+                        cudaStream_t st) {
+    return launch_gemm2_ew<EPI, 8>(tmA, tmB, om, p, grid, st);
 }
-static int dispatch_epi2(int epi, const CUtensorMap& a, const CUtensorMap& b, const GemmParams& p, int grid, cudaStream_t st) {
+static int dispatch_epi2(int epi, const CUtensorMap& a, const CUtensorMap& b, const OutMaps& om, const GemmParams& p, int grid,
+                         cudaStream_t st) {
     switch (epi) {
-        case EPI_BF16: return launch_gemm2<EPI_BF16>(a, b, p, grid, st);
-        case EPI_GELU: return launch_gemm2<EPI_GELU>(a, b, p, grid, st);
-        case EPI_RESID_F32: return launch_gemm2<EPI_RESID_F32>(a, b, p, grid, st);
-        case EPI_RESID_BF16: return launch_gemm2<EPI_RESID_BF16>(a, b, p, grid, st);
-        case EPI_ACCUM_F32: return launch_gemm2<EPI_ACCUM_F32>(a, b, p, grid, st);
-        case EPI_DGELU: return launch_gemm2<EPI_DGELU>(a, b, p, grid, st);
-        case EPI_F32: return launch_gemm2<EPI_F32>(a, b, p, grid, st);
+        case EPI_BF16: return launch_gemm2<EPI_BF16>(a, b, om, p, grid, st);
+        case EPI_GELU: return launch_gemm2<EPI_GELU>(a, b, om, p, grid, st);
+        case EPI_RESID_F32: return launch_gemm2<EPI_RESID_F32>(a, b, om, p, grid, st);
+        case EPI_RESID_BF16: return launch_gemm2<EPI_RESID_BF16>(a, b, om, p, grid, st);
+        case EPI_ACCUM_F32: return launch_gemm2<EPI_ACCUM_F32>(a, b, om, p, grid, st);
+        case EPI_DGELU: return launch_gemm2<EPI_DGELU>(a, b, om, p, grid, st);
+        case EPI_F32: return launch_gemm2<EPI_F32>(a, b, om, p, grid, st);
     }
     set_error("gemm_bf16: unknown epilogue %d", epi);
     return PENROZ_ERR_ARG;
@@ -972,7 +1246,15 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     const long long u_pair = ceil_div(M, 2 * BM) * ceil_div(N, 256);
     const long long u_256 = (long long)tiles_m * ceil_div(N, 256);
     const long long u_128 = (long long)tiles_m * ceil_div(N, 128);
-    const bool pair_ok = (M >= 256) && (N > 128) && (sms >= 2) && !(flags & 16);
+    // the pair kernel writes its output with bulk tensor stores: 16-byte aligned base and row pitch
+    const bool out_f32 = (epilogue == EPI_RESID_F32 || epilogue == EPI_ACCUM_F32 || epilogue == EPI_F32);
+    const size_t oesz = out_f32 ? 4 : 2;
+    const bool tma_out_ok = ((uintptr_t)out % 16 == 0) && ((size_t)ldo * oesz % 16 == 0) &&
+                            (epilogue != EPI_GELU || (((uintptr_t)out2 % 16 == 0) && ((size_t)ldo2 * 2 % 16 == 0))) &&
+                            (epilogue != EPI_RESID_F32 || (((uintptr_t)aux % 16 == 0) && ((size_t)ldaux * 4 % 16 == 0))) &&
+                            ((epilogue != EPI_RESID_BF16 && epilogue != EPI_DGELU) ||
+                             (((uintptr_t)aux % 16 == 0) && ((size_t)ldaux * 2 % 16 == 0)));
+    const bool pair_ok = (M >= 256) && (N > 128) && (sms >= 2) && !(flags & 16) && tma_out_ok;
     const double c_pair = pair_ok ? (double)ceil_div(u_pair, sms / 2) * 1.0 : 1e30;
     const double c_256 = (N > 128) ? (double)ceil_div(u_256, sms) * 1.12 : 1e30;
     const double c_128 = (double)ceil_div(u_128, sms) * 0.5 * 1.35;
@@ -1018,8 +1300,21 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     if (rc) return rc;
 
     if (pair) {
+        OutMaps om;
+        rc = encode_out_2d(&om.o, out, out_f32, (uint64_t)N, (uint64_t)M, (uint64_t)ldo);
+        if (rc) return rc;
+        if (epilogue == EPI_GELU) {
+            rc = encode_out_2d(&om.o2, out2, false, (uint64_t)N, (uint64_t)M, (uint64_t)ldo2);
+            if (rc) return rc;
+        } else if (epilogue == EPI_RESID_F32 || epilogue == EPI_RESID_BF16 || epilogue == EPI_DGELU) {
+            // the aux operand, loaded box by box
+            rc = encode_out_2d(&om.o2, aux, epilogue == EPI_RESID_F32, (uint64_t)N, (uint64_t)M, (uint64_t)ldaux);
+            if (rc) return rc;
+        } else {
+            om.o2 = om.o;
+        }
         const int units2 = p.tiles_m * p.tiles_n * p.splits;
-        return dispatch_epi2(epilogue, tmA, tmB, p, 2 * min(units2, workers), st);
+        return dispatch_epi2(epilogue, tmA, tmB, om, p, 2 * min(units2, workers), st);
     }
     const int units = p.tiles_m * p.tiles_n * p.splits;
     const int grid = min(units, sms);
