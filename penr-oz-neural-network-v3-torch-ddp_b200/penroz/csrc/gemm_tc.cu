@@ -1279,8 +1279,22 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     p.splits = 1;
     const int workers = pair ? sms / 2 : sms;
     if (epilogue == EPI_ACCUM_F32) {
+        // split K so that the units fill whole waves of the workers: the fewest splits that leave the last wave at
+        // least 95 % full (27 tiles of the 2304 x 768 QKV gradient: 8 splits = 216 units on 74 CTA pairs, not 2 = 54),
+        // each split at least 8 k-blocks deep
         const int tiles = p.tiles_m * p.tiles_n;
-        if (tiles < workers) p.splits = max(1, min(p.kb_total, workers / tiles));
+        if (tiles < workers) {
+            const int smax = max(1, min(p.kb_total / 8, 4 * workers / tiles));
+            int best = 1;
+            double best_eff = 0.0;
+            for (int sp = 1; sp <= smax; ++sp) {
+                const int units = tiles * sp;
+                const double eff = (double)units / (double)(((units + workers - 1) / workers) * workers);
+                if (eff > best_eff + 1e-9) { best_eff = eff; best = sp; }
+                if (eff >= 0.95) { best = sp; break; }
+            }
+            p.splits = best;
+        }
         // red.add accumulates into `out`: with beta == 0 the caller must have zeroed it
         if (p.splits > 1 && !p.beta) {
             cudaError_t e = cudaMemset2DAsync(out, (size_t)ldo * 4, 0, (size_t)N * 4, (size_t)M, st);
