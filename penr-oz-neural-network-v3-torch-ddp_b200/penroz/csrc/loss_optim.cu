@@ -91,39 +91,52 @@ ce_rows_kernel(T* __restrict__ logits, long long ld, const long long* __restrict
     }
 }
 
-// bf16 rows that fit in shared memory (V * 2 bytes <= ~110 KB, two CTAs per SM): the row is read from HBM ONCE into
-// smem while (max, sum-exp) are accumulated, then the gradient is produced from the smem copy. Algorithmic traffic
-// per row: V*2 read + V*2 written (the two-pass kernel above reads the row twice).
+// The training form for bf16 logits (16-byte aligned rows, gradient written). Same two passes, built for the two
+// limits the generic kernel runs into at V = 50257 (1.65 G elements per step): the SFU (one ex2 per element and pass,
+// 0.39 ms each on 148 SMs) and issue slots (15 per element there). Here: the running maximum is rescaled only when it
+// moves (a branch taken a handful of times per thread instead of an ex2 per vector), the exponent's argument is one
+// packed FMA (x log2e - m log2e), sums and the gradient scale are packed too, the gradient is packed with cvt.bf16x2,
+// and the target column is patched by one thread after the pass instead of being tested for on every element.
 __global__ void __launch_bounds__(512)
-ce_rows_smem_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const long long* __restrict__ tgt, int V,
+ce_rows_bf16_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const long long* __restrict__ tgt, int V,
                     long long ignore_index, const int* __restrict__ n_valid, float grad_scale,
                     float* __restrict__ loss_rows, int* __restrict__ err_flag) {
-    extern __shared__ uint4 rowbuf[];
     __shared__ float red[32];
+    constexpr float kLog2e = 1.44269504088896340736f;
     const int row = blockIdx.x;
     __nv_bfloat16* x = logits + (size_t)row * ld;
     const long long t = tgt[row];
     const bool ignored = (t == ignore_index);
-    if (!ignored && (t < 0 || t >= V)) {
+    const bool t_ok = !ignored && t >= 0 && t < V;
+    if (!ignored && !t_ok) {
         if (threadIdx.x == 0 && err_flag) atomicExch(err_flag, 2);
     }
     const int nvec = V >> 3;
     uint4* x4 = reinterpret_cast<uint4*>(x);
-    float m = -INFINITY, s = 0.f;
+    float m = -INFINITY;
+    f32x2 s2 = f2_all(0.f);
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-        Vec16<__nv_bfloat16> v;
-        v.raw = x4[i];
-        rowbuf[i] = v.raw;
-        float lm = v.get(0);
+        const uint4 raw = x4[i];
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+        float lo[4], hi[4];
 #pragma unroll
-        for (int k = 1; k < 8; ++k) lm = fmaxf(lm, v.get(k));
-        const float nm = fmaxf(m, lm);
-        float acc = 0.f;
+        for (int k = 0; k < 4; ++k) { lo[k] = __uint_as_float(w[k] << 16); hi[k] = __uint_as_float(w[k] & 0xffff0000u); }
+        const float lm = fmaxf(fmaxf(fmaxf(lo[0], hi[0]), fmaxf(lo[1], hi[1])), fmaxf(fmaxf(lo[2], hi[2]), fmaxf(lo[3], hi[3])));
+        if (lm > m) {   // rare after the first vectors
+            const float r = ex2_fast((m - lm) * kLog2e);   // m = -inf: 0
+            s2 = f2_mul(s2, f2_all(r));
+            m = lm;
+        }
+        const f32x2 off = f2_all(-m * kLog2e);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc += __expf(v.get(k) - nm);
-        s = s * __expf(m - nm) + acc;
-        m = nm;
+        for (int k = 0; k < 4; ++k) {
+            float a0, a1;
+            f2_unpack(f2_fma(f2_pack(lo[k], hi[k]), f2_all(kLog2e), off), a0, a1);
+            s2 = f2_add(s2, f2_pack(ex2_fast(a0), ex2_fast(a1)));
+        }
     }
+    float s;
+    { float s0, s1; f2_unpack(s2, s0, s1); s = s0 + s1; }
     for (int i = nvec * 8 + threadIdx.x; i < V; i += blockDim.x) {   // < 8 tail elements
         const float v = __bfloat162float(x[i]);
         const float nm = fmaxf(m, v);
@@ -134,29 +147,30 @@ ce_rows_smem_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const long
     const float part = (m == -INFINITY) ? 0.f : s * __expf(m - gm);
     const float gs = block_sum(part, red);
     const float lse = gm + logf(gs);
+    float xt = 0.f;
     if (threadIdx.x == 0) {
-        float l = 0.f;
-        if (!ignored && t >= 0 && t < V) l = lse - __bfloat162float(x[t]);
-        loss_rows[row] = l;
+        if (t_ok) xt = __bfloat162float(x[t]);
+        loss_rows[row] = t_ok ? lse - xt : 0.f;
     }
-    __syncthreads();  // x[t] read above before the row is overwritten
     const float scale = ignored ? 0.f : grad_scale / (float)max(1, *n_valid);
+    const f32x2 off = f2_all(-lse * kLog2e), sc2 = f2_all(scale);
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-        Vec16<__nv_bfloat16> v;
-        v.raw = rowbuf[i];
+        const uint4 raw = x4[i];   // served from L2
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+        uint32_t o[4];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            float p = __expf(v.get(k) - lse);
-            if ((long long)(i * 8 + k) == t) p -= 1.f;
-            v.set(k, p * scale);
+        for (int k = 0; k < 4; ++k) {
+            float a0, a1, p0, p1;
+            f2_unpack(f2_fma(f2_pack(__uint_as_float(w[k] << 16), __uint_as_float(w[k] & 0xffff0000u)), f2_all(kLog2e), off), a0, a1);
+            f2_unpack(f2_mul(f2_pack(ex2_fast(a0), ex2_fast(a1)), sc2), p0, p1);
+            o[k] = pack_bf16x2(p0, p1);
         }
-        x4[i] = v.raw;
+        x4[i] = make_uint4(o[0], o[1], o[2], o[3]);
     }
-    for (int i = nvec * 8 + threadIdx.x; i < V; i += blockDim.x) {
-        float p = __expf(__bfloat162float(x[i]) - lse);
-        if ((long long)i == t) p -= 1.f;
-        x[i] = __float2bfloat16_rn(p * scale);
-    }
+    for (int i = nvec * 8 + threadIdx.x; i < V; i += blockDim.x)
+        x[i] = __float2bfloat16_rn(__expf(__bfloat162float(x[i]) - lse) * scale);
+    __syncthreads();   // the pass has written column t
+    if (threadIdx.x == 0 && t_ok) x[t] = __float2bfloat16_rn((__expf(xt - lse) - 1.f) * scale);
 }
 
 // loss = sum(loss_rows) / n_valid, single CTA, fixed order (deterministic); *loss_out (+)= loss * out_scale
@@ -357,20 +371,9 @@ extern "C" int penroz_ce_rows(void* logits, long long ld, const long long* targe
     PENROZ_REQUIRE(logits && targets && loss_rows && n_valid, "ce_rows: null argument");
     cudaStream_t st = (cudaStream_t)stream;
     const int threads = V >= 8192 ? 512 : (V >= 1024 ? 256 : 64);
-    const size_t row_smem = ((size_t)(V >> 3)) * 16;
-    // measured on B200: 395 us per 6144 x 50257 chunk against 296 us for the two-pass kernel (whose second read mostly
-    // hits L2), so the staged variant stays opt-in
-    static const bool use_smem_rows = getenv("PENROZ_CE_SMEM") != nullptr;
-    if (use_smem_rows && dtype == BF16 && write_grad && V >= 4096 && row_smem <= 110 * 1024 && (ld % 8 == 0) && ((uintptr_t)logits % 16 == 0)) {
-        static std::atomic<int> configured{0};
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (!((configured.load() >> dev) & 1)) {
-            cudaError_t e = cudaFuncSetAttribute(ce_rows_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
-            if (e != cudaSuccess) { set_error("ce_rows: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
-            configured.fetch_or(1 << dev);
-        }
-        ce_rows_smem_kernel<<<M, 512, row_smem, st>>>((__nv_bfloat16*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, err_flag);
+    static const bool generic = getenv("PENROZ_CE_GENERIC") != nullptr;   // A/B switch
+    if (!generic && dtype == BF16 && write_grad && V >= 4096 && (ld % 8 == 0) && ((uintptr_t)logits % 16 == 0)) {
+        ce_rows_bf16_kernel<<<M, 512, 0, st>>>((__nv_bfloat16*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, err_flag);
     } else if (dtype == BF16)
         ce_rows_kernel<__nv_bfloat16><<<M, threads, 0, st>>>((__nv_bfloat16*)logits, ld, targets, V, ignore_index, n_valid, grad_scale, loss_rows, write_grad, err_flag);
     else if (dtype == F32)
