@@ -43,7 +43,9 @@ extern "C" {
 #define PENROZ_EPI_RESID_F32 2  /* out(f32) = aux(f32) + float(T(acc + bias))              */
 #define PENROZ_EPI_RESID_BF16 3 /* out(bf16) = bf16(float(aux) + float(bf16(acc + bias)))  */
 #define PENROZ_EPI_ACCUM_F32 4  /* out(f32) (+)= acc   (flags bit 1 = accumulate)          */
-#define PENROZ_EPI_DGELU 5      /* out = T(T(acc) * gelu'(aux))                            */
+#define PENROZ_EPI_DGELU 5      /* out = T(T(acc) * gelu'(aux)); penroz_gemm_bf16: a non-null out2 is an fp32 [N]
+                                   vector that receives += the column sums of out (bias gradient of the Linear in
+                                   front of the activation)                                 */
 #define PENROZ_EPI_F32 6        /* out(f32) = acc + bias                                   */
 /* flags: bit0 tanh-GELU (else erf), bit1 accumulate into out, bit2 force 128-wide tile, bit3 force 256-wide tile */
 
@@ -145,11 +147,13 @@ int penroz_attn_bwd_simt(const void* qkv, const void* out, const void* dout, con
 
 /* ---- the same attention on the tensor cores (bf16, head_dim 64): tcgen05.mma with S / dP / dK / dV / dQ in TMEM,
  * q, k, v and dO tiles fetched from the packed buffers by TMA. Replaces the same reference lines as above for the
- * bf16-autocast training step. The backward needs scratch (row dot-products + an fp32 dQ accumulator it zeroes). */
+ * bf16-autocast training step. The backward needs scratch (row dot-products + an fp32 dQ accumulator it zeroes).
+ * dbias (optional, fp32 [3C]) receives += the column sums of dqkv as written (bf16): the bias gradient of the QKV Linear
+ * (nn.Linear backward, mappers.py:156), summed where dK, dV and dQ leave the kernels instead of by a pass over dqkv. */
 int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
 size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D);
-int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int B, int T,
-                       int H, int D, void* scratch, size_t scratch_bytes, void* stream);
+int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* dbias,
+                       int B, int T, int H, int D, void* scratch, size_t scratch_bytes, void* stream);
 
 /* ---- softmax cross-entropy over a chunk of logits rows ----
  * Replaces F.cross_entropy(logits.view(-1,V), target.view(-1)) (neural_net_model.py:264-267): mean over rows whose

@@ -450,17 +450,27 @@ __global__ void attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const
     }
 }
 
-// dq_accum (fp32 [rows, C]) -> bf16 into the q third of dqkv [rows, 3C]
-__global__ void attn_bwd_dq_finish_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, size_t rows,
-                                          int C) {
-    const size_t n4 = rows * (size_t)C / 4;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
-        const float4 v = reinterpret_cast<const float4*>(acc)[i];
-        const size_t e = i * 4, r = e / C, c = e % C;
-        uint2 w;
-        w.x = pack_bf16x2(v.x, v.y);
-        w.y = pack_bf16x2(v.z, v.w);
-        *reinterpret_cast<uint2*>(dqkv + r * 3 * (size_t)C + c) = w;
+// dq_accum (fp32 [rows, C]) -> bf16 into the q third of dqkv [rows, 3C]. A thread keeps the same 4 columns over its
+// CTA's rows (blockIdx.x, + gridDim.x, ...), so with dbias it also carries their column sums (of the rounded values,
+// as the bias gradient of the QKV Linear wants them) and adds them once at the end.
+__global__ void __launch_bounds__(256)
+attn_bwd_dq_finish_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, size_t rows, int C,
+                          float* __restrict__ dbias) {
+    for (int c = threadIdx.x * 4; c < C; c += blockDim.x * 4) {
+        float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (size_t r = blockIdx.x; r < rows; r += gridDim.x) {
+            const float4 v = *reinterpret_cast<const float4*>(acc + r * C + c);
+            uint2 w;
+            w.x = pack_bf16x2(v.x, v.y);
+            w.y = pack_bf16x2(v.z, v.w);
+            *reinterpret_cast<uint2*>(dqkv + r * 3 * (size_t)C + c) = w;
+            const float2 a = unpack_bf16x2(w.x), b = unpack_bf16x2(w.y);
+            cs.x += a.x; cs.y += a.y; cs.z += b.x; cs.w += b.y;
+        }
+        if (dbias) {
+            atomicAdd(dbias + c, cs.x); atomicAdd(dbias + c + 1, cs.y);
+            atomicAdd(dbias + c + 2, cs.z); atomicAdd(dbias + c + 3, cs.w);
+        }
     }
 }
 
@@ -485,7 +495,8 @@ __global__ void __launch_bounds__(576, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const __grid_constant__ CUtensorMap tmDQ,
                    const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
-                   __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2e) {
+                   __nv_bfloat16* __restrict__ dqkv, float* __restrict__ dbias, int Tn, int H, float scale,
+                   float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
@@ -719,16 +730,27 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             __syncwarp();
             tmem_ld_32x16((which == 0 ? tDV : tDK) + lane_addr + part * 16, v);
             tmem_ld_wait();
+            uint32_t w[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) w[k] = pack_bf16x2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
             if (key_ok) {
                 __nv_bfloat16* dst = which == 0 ? gv : gk;
+                *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+                *reinterpret_cast<uint4*>(dst + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+            }
+            if (dbias) {
+                // bias gradient of the QKV Linear: column sums of the rounded dK / dV over this warp's 32 keys (once
+                // per key tile), one red.add per column from lane 0
 #pragma unroll
-                for (int k = 0; k < 16; k += 8) {
-                    uint4 w;
-                    w.x = pack_bf16x2(__uint_as_float(v[k]), __uint_as_float(v[k + 1]));
-                    w.y = pack_bf16x2(__uint_as_float(v[k + 2]), __uint_as_float(v[k + 3]));
-                    w.z = pack_bf16x2(__uint_as_float(v[k + 4]), __uint_as_float(v[k + 5]));
-                    w.w = pack_bf16x2(__uint_as_float(v[k + 6]), __uint_as_float(v[k + 7]));
-                    *reinterpret_cast<uint4*>(dst + k) = w;
+                for (int k = 0; k < 8; ++k) {
+                    float2 c = key_ok ? unpack_bf16x2(w[k]) : make_float2(0.f, 0.f);
+                    c.x = warp_sum(c.x);
+                    c.y = warp_sum(c.y);
+                    if (lane == 0) {
+                        float* db = dbias + (which == 0 ? 2 : 1) * C + h * AT_D + part * 16 + 2 * k;
+                        atomicAdd(db, c.x);
+                        atomicAdd(db + 1, c.y);
+                    }
                 }
             }
         }
@@ -828,7 +850,8 @@ extern "C" size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D) {
 // dqkv [B,T,3C] <- gradient of causal attention wrt the packed QKV buffer. scratch: delta [B,H,T] + dq accumulator
 // [B*T, C] fp32 (zeroed here with cudaMemsetAsync on `stream`).
 extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
-                                  int B, int T, int H, int D, void* scratch, size_t scratch_bytes, void* stream) {
+                                  float* dbias, int B, int T, int H, int D, void* scratch, size_t scratch_bytes,
+                                  void* stream) {
     PENROZ_REQUIRE(B > 0 && T > 0 && H > 0, "attn_bwd_tc: bad shape");
     PENROZ_REQUIRE(D == 64, "attn_bwd_tc: head_dim %d unsupported (tensor-core path is head_dim 64)", D);
     PENROZ_REQUIRE(B <= 65535 && H <= 65535, "attn_bwd_tc: B/H too large for the launch grid");
@@ -862,11 +885,12 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     attn_bwd_delta_kernel<<<(unsigned)((pairs * 8 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
-    attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, tmDQ, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
-    size_t n4 = rows * C / 4;
-    size_t g = (n4 + 255) / 256;
-    size_t cap = (size_t)num_sms() * 16;
-    attn_bwd_dq_finish_kernel<<<(unsigned)(g > cap ? cap : g), 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, C);
+    attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, tmDQ, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, dbias, T, H, scale, scale * 1.44269504088896340736f);
+    {
+        const int threads = (C / 4 >= 256) ? 256 : ((C / 4 + 31) / 32 * 32);
+        size_t cap = (size_t)num_sms() * 8;
+        attn_bwd_dq_finish_kernel<<<(unsigned)(rows < cap ? rows : cap), threads, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, C, dbias);
+    }
     count_launch(3);
     return check_launch("attn_bwd_tc");
 }

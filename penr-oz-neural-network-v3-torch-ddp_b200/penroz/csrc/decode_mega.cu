@@ -415,7 +415,7 @@ static bool mega_enabled() {
 size_t decode_mega_extra_bytes(int B, int H) { (void)B; (void)H; return MEGA_SYNC_BYTES + 256; }
 
 bool decode_mega_supported(int B, int C, int H, int V, int F, int n_layer, int dtype) {
-    if (!mega_enabled() || dtype != BF16 || B < 1 || B > 64 || C % H || n_layer > MEGA_MAX_LAYERS) return false;
+    if (!mega_enabled() || dtype != BF16 || B < 1 || B > 16 || C % H || n_layer > MEGA_MAX_LAYERS) return false;
     const int D = C / H;
     if (C % 32 || F % 32 || D % 8) return false;
     const int lpk = D / 8;
@@ -477,7 +477,7 @@ int decode_step_mega(const long long* tokens, const void* wte, const void* wpe, 
         }                                                                                                            \
         if (e == cudaSuccess) e = cudaLaunchCooperativeKernel((const void*)k, dim3(grid), dim3(WS_THREADS), args, smem, st); \
     }
-    if (nt == 1) PENROZ_MEGA(1, 0) else if (nt == 2) PENROZ_MEGA(2, 1) else if (nt == 4) PENROZ_MEGA(4, 2) else PENROZ_MEGA(8, 3)
+    if (nt == 1) PENROZ_MEGA(1, 0) else PENROZ_MEGA(2, 1)
 #undef PENROZ_MEGA
     if (e != cudaSuccess) { set_error("gpt2_decode_step (persistent): %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
     count_launch();

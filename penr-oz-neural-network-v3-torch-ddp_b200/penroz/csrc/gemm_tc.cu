@@ -498,6 +498,21 @@ __device__ __forceinline__ void epilogue_chunk_box(const GemmParams& p, const ui
         }
 #pragma unroll
         for (uint32_t j = 0; j < 4; ++j) sts128(row + ((j ^ x) << 4), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+        if (EPI == EPI_DGELU && p.out2 != nullptr) {
+            // column sums of the chunk as its consumers see it (bf16), for the bias gradient of the Linear in front of
+            // the activation: lane = column, down the 32 rows of the box (rows past M hold zeros: their A rows and
+            // their aux rows were zero-filled by the loads), then one red.add per column
+            __syncwarp();
+            const uint32_t cb = box + (((uint32_t)lane & 7u) << 1), piece = (uint32_t)lane >> 3;
+            float cs = 0.f;
+#pragma unroll
+            for (uint32_t r = 0; r < 32; ++r) {
+                unsigned short hv;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hv) : "r"(cb + r * 64u + ((piece ^ ((r >> 1) & 3u)) << 4)) : "memory");
+                cs += __uint_as_float((uint32_t)hv << 16);
+            }
+            if (col0 + lane < p.N) atomicAdd(reinterpret_cast<float*>(p.out2) + col0 + lane, cs);
+        }
     }
 }
 
@@ -1137,6 +1152,19 @@ static int encode_out_2d(CUtensorMap* tm, const void* ptr, bool f32, uint64_t co
     return PENROZ_OK;
 }
 
+// out[c] += sum_r x[r, c] for a bf16 matrix: the bias-gradient side output of EPI_DGELU for the shapes that do not
+// take the pair kernel (small problems: one thread per column pair and row slab, red.add)
+__global__ void colsum_atomic_bf16_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int rows, int N,
+                                          float* __restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= N) return;
+    const int per = (rows + gridDim.y - 1) / gridDim.y;
+    const int r0 = blockIdx.y * per, r1 = min(rows, r0 + per);
+    float s = 0.f;
+    for (int r = r0; r < r1; ++r) s += __bfloat162float(x[(long long)r * ld + c]);
+    if (r1 > r0) atomicAdd(out + c, s);
+}
+
 template <int BN, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
@@ -1332,7 +1360,14 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     }
     const int units = p.tiles_m * p.tiles_n * p.splits;
     const int grid = min(units, sms);
-    if (bn == 256) return dispatch_epi<256>(epilogue, tmA, tmB, p, grid, st);
-    if (bn == 64) return dispatch_epi<64>(epilogue, tmA, tmB, p, grid, st);
-    return dispatch_epi<128>(epilogue, tmA, tmB, p, grid, st);
+    if (bn == 256) rc = dispatch_epi<256>(epilogue, tmA, tmB, p, grid, st);
+    else if (bn == 64) rc = dispatch_epi<64>(epilogue, tmA, tmB, p, grid, st);
+    else rc = dispatch_epi<128>(epilogue, tmA, tmB, p, grid, st);
+    if (rc == PENROZ_OK && epilogue == EPI_DGELU && out2 != nullptr) {
+        dim3 g((N + 127) / 128, (unsigned)min(64, (M + 63) / 64));
+        colsum_atomic_bf16_kernel<<<g, 128, 0, st>>>((const __nv_bfloat16*)out, ldo, M, N, (float*)out2);
+        count_launch();
+        rc = check_launch("gemm_bf16/colsum");
+    }
+    return rc;
 }

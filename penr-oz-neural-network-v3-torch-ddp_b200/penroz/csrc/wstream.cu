@@ -1,4 +1,4 @@
-// Weight-streaming Linear for the decode step, 1 <= M <= 64 activation rows, bf16.
+// Weight-streaming Linear for the decode step, 1 <= M <= 64 activation rows (a CTA takes up to 16 of them), bf16.
 //
 // A decode-step Linear reads its whole weight matrix once for a handful of activation rows: 247 MB of weights per GPT-2
 // 124M token step against 64 x 768 activations. It is bound by how evenly and how early all 148 SMs pull weight bytes,
@@ -31,8 +31,20 @@ namespace penroz {
 // Dynamic shared memory: xs[8 NT][kchunk + WS_XPAD] bf16 | red[WS_WARPS][8 NT][16] fp32
 template <int NT>
 __global__ void __launch_bounds__(WS_THREADS, 1)
-wstream_linear_kernel(const WsParams p, int kchunk) {
+wstream_linear_kernel(const WsParams p0, int kchunk) {
     extern __shared__ __align__(16) unsigned char ws_smem[];
+    // blockIdx.y = group of 8 NT activation rows: everything indexed by row moves with it
+    WsParams p = p0;
+    if (gridDim.y > 1) {
+        const int r0 = blockIdx.y * 8 * NT;
+        p.M = min(8 * NT, p0.M - r0);
+        p.x = p0.x + (size_t)r0 * p0.ldx;
+        p.out = p0.out + (size_t)r0 * p0.ldo;
+        if (p0.aux) p.aux = p0.aux + (size_t)r0 * p0.ldaux;
+        if (p0.bt) p.bt = p0.bt + (size_t)r0 * p0.max_pages;
+        if (p0.amax_val) { p.amax_val = p0.amax_val + (size_t)r0 * gridDim.x; p.amax_idx = p0.amax_idx + (size_t)r0 * gridDim.x; }
+        if (p0.tok) { p.tok = p0.tok + r0; if (p0.emb_out) p.emb_out = p0.emb_out + (size_t)r0 * p0.K; }
+    }
     constexpr int MB = 8 * NT;
     const int kc = min(kchunk, p.K);
     const int xstride = kc + WS_XPAD;
@@ -52,15 +64,24 @@ static bool ws_use_pdl() {
     return on;
 }
 
-int ws_nt(int M) { return M <= 8 ? 1 : (M <= 16 ? 2 : (M <= 32 ? 4 : 8)); }
+int ws_nt(int M) { return M <= 8 ? 1 : 2; }   // rows per CTA / 8 (see ws_groups)
 
 // CTAs the launch uses for N output columns (= arg-max candidates per row)
+// more than 16 activation rows run as groups of 16 (blockIdx.y): a CTA then stages and normalises 16 rows instead of
+// all of them (measured at 64 rows: every one of 144 CTAs spent most of its 18 us on LayerNorm and staging of the same
+// 64 x 768 activations) and streams 4 units of weights instead of one; the groups' reads of a weight row meet in L2
+int ws_groups(int M) { return M > 16 ? (M + 15) / 16 : 1; }
+
 int wstream_grid(int M, int N) {
     const int nunits = (N + 15) / 16;
+    if (M > 16) {
+        const int cap = max(1, num_sms() / ws_groups(M));
+        return nunits < cap ? nunits : cap;
+    }
     // measured at batch 1 (124M head, 3142 units): 4 CTAs per SM's worth of shorter unit loops beat one resident CTA per
     // SM looping 21 times (322 vs 369 us per token step), although the extra CTAs run as later waves
     static const int small_per_sm = getenv("PENROZ_WS_PER_SM") ? atoi(getenv("PENROZ_WS_PER_SM")) : 1;
-    const int cap = num_sms() * (ws_nt(M) >= 4 ? 1 : small_per_sm);
+    const int cap = num_sms() * small_per_sm;
     return nunits < cap ? nunits : cap;
 }
 
@@ -94,14 +115,14 @@ int launch_wstream(const WsParams& p, cudaStream_t st) {
     PENROZ_REQUIRE(!p.tok || kchunk >= p.K, "wstream_linear: embedding prologue needs the whole row staged");
     const int grid = wstream_grid(p.M, p.N);
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(WS_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cfg.gridDim = dim3(grid, ws_groups(p.M)); cfg.blockDim = dim3(WS_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = ws_use_pdl() ? 1 : 0;
     cudaError_t e = cudaSuccess;
     // cudaFuncSetAttribute costs microseconds of host time: raise a kernel's limit only when a launch needs more
-    static std::atomic<int> granted[4][64];
+    static std::atomic<int> granted[2][64];
     int dev = 0;
     cudaGetDevice(&dev);
 #define PENROZ_WS(NTV, SLOT)                                                                                         \
@@ -113,7 +134,7 @@ int launch_wstream(const WsParams& p, cudaStream_t st) {
         }                                                                                                            \
         if (e == cudaSuccess) e = cudaLaunchKernelEx(&cfg, k, p, kchunk);                                            \
     }
-    if (nt == 1) PENROZ_WS(1, 0) else if (nt == 2) PENROZ_WS(2, 1) else if (nt == 4) PENROZ_WS(4, 2) else PENROZ_WS(8, 3)
+    if (nt == 1) PENROZ_WS(1, 0) else PENROZ_WS(2, 1)
 #undef PENROZ_WS
     if (e != cudaSuccess) { set_error("wstream_linear launch: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
     count_launch();

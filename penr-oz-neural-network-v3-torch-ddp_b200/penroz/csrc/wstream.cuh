@@ -298,91 +298,8 @@ __device__ __forceinline__ void ws_stage_rows_general_impl(const WsParams& p, __
 }
 
 template <int NT>
-__device__ __noinline__ void ws_stage_rows_general(const WsParams& p, __nv_bfloat16* xs, int xstride, int k0, int kc) {
-    ws_stage_rows_general_impl<NT>(p, xs, xstride, k0, kc);
-}
-
-// The common case inline (plain rows, or LayerNorm over rows of at most 1024 columns staged whole); embedding rows,
-// LayerNorm over longer or chunk-staged rows go through the general routine above.
-template <int NT>
 __device__ __forceinline__ void ws_stage_rows(const WsParams& p, __nv_bfloat16* xs, int xstride, int k0, int kc) {
-    // few rows (NT < 4): LayerNorm out of shared memory in the general routine -- it keeps this kernel's register count low
-    // enough for several CTAs per SM, which is what keeps enough weight bytes in flight at small batch
-    if (NT < 4) { ws_stage_rows_general_impl<NT>(p, xs, xstride, k0, kc); return; }     // small kernels: all inline
-    if (p.tok || (p.ln && (kc < p.K || p.K > 1024))) { ws_stage_rows_general<NT>(p, xs, xstride, k0, kc); return; }
-    constexpr int MB = 8 * NT;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int kv8 = kc >> 3, total = MB * kv8;
-    for (int e = tid; e < total; e += WS_THREADS) {
-        const int r = e / kv8, c = e - r * kv8;
-        __nv_bfloat16* dst = xs + (size_t)r * xstride + c * 8;
-        if (r < p.M) cp_async16(dst, p.x + (size_t)r * p.ldx + k0 + c * 8);
-        else *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
-    }
-    cp_async_wait_all();
-    __syncthreads();
-    if (!p.ln) return;
-    const int K = p.K;
-        // A lane owns the same <= 4 16-byte column slices in every row: gamma and beta are unpacked once, a row's
-        // values stay in registers from the first statistics pass to the store (one shared-memory read and one
-        // write per element, ~6 instructions per element)
-        uint4 gp[4], bp[4];      // kept packed: 8 registers per slice instead of 16
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int k = lane * 8 + 256 * i;
-            gp[i] = make_uint4(0, 0, 0, 0); bp[i] = make_uint4(0, 0, 0, 0);
-            if (k < K) {
-                gp[i] = *reinterpret_cast<const uint4*>(p.ln_w + k);
-                if (p.ln_b) bp[i] = *reinterpret_cast<const uint4*>(p.ln_b + k);
-            }
-        }
-        const float inv_k = 1.f / (float)K;
-        for (int r = warp; r < p.M; r += WS_WARPS) {
-            __nv_bfloat16* row = xs + (size_t)r * xstride;
-            float xv[4][8];
-            float s = 0.f;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int k = lane * 8 + 256 * i;
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (k < K) v = *reinterpret_cast<const uint4*>(row + k);
-                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 f = unpack_bf16x2(w[j]);
-                    xv[i][2 * j] = f.x; xv[i][2 * j + 1] = f.y;
-                    s += f.x + f.y;
-                }
-            }
-            const float mean = warp_sum(s) * inv_k;
-            float q = 0.f;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const bool on = lane * 8 + 256 * i < K;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    xv[i][j] -= mean;
-                    if (on) q = fmaf(xv[i][j], xv[i][j], q);
-                }
-            }
-            const float rstd = rsqrtf(warp_sum(q) * inv_k + p.ln_eps);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int k = lane * 8 + 256 * i;
-                if (k < K) {
-                    const uint32_t gws[4] = {gp[i].x, gp[i].y, gp[i].z, gp[i].w};
-                    const uint32_t gbs[4] = {bp[i].x, bp[i].y, bp[i].z, bp[i].w};
-                    uint32_t o[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const float2 a2 = unpack_bf16x2(gws[j]), b2 = unpack_bf16x2(gbs[j]);
-                        o[j] = pack_bf16x2(fmaf(xv[i][2 * j] * rstd, a2.x, b2.x), fmaf(xv[i][2 * j + 1] * rstd, a2.y, b2.y));
-                    }
-                    *reinterpret_cast<uint4*>(row + k) = make_uint4(o[0], o[1], o[2], o[3]);
-                }
-            }
-        }
-        __syncthreads();
+    ws_stage_rows_general_impl<NT>(p, xs, xstride, k0, kc);
 }
 
 // One Linear for this CTA: units first_unit, first_unit + unit_stride, ... of 16 weight rows each.

@@ -500,15 +500,14 @@ class Gpt2Engine:
             # ---- MLP branch
             dh = buf("dh", (M, F), act)
             ops.gemm(dy, self._wb(blk.proj2.weight), b_layout=1, epilogue=EPI_DGELU, aux=s["h"], out=dh,
-                     tanh=blk.gelu_tanh)
+                     tanh=blk.gelu_tanh, colsum_out=None if blk.fc.bias is None else fl.grad(blk.fc.bias),
+                     colsum_scratch=scratch)
             ops.gemm(dy, s["g"], a_layout=1, b_layout=1, epilogue=EPI_ACCUM_F32, out=fl.grad(blk.proj2.weight),
                      accumulate=True)
             d_ln2 = buf("d_ln", (M, C), act)
             ops.gemm(dh, self._wb(blk.fc.weight), b_layout=1, out=d_ln2)
             ops.gemm(dh, s["ln2"], a_layout=1, b_layout=1, epilogue=EPI_ACCUM_F32, out=fl.grad(blk.fc.weight),
                      accumulate=True)
-            if blk.fc.bias is not None:
-                ops.colsum(dh, fl.grad(blk.fc.bias), accumulate=True, scratch=scratch)
             ops.layernorm_bwd(d_ln2, s["xmid"], blk.ln2.weight.data, s["m2"], s["r2"], add=dx,
                               dgamma=fl.grad(blk.ln2.weight), dbeta=None if blk.ln2.bias is None else fl.grad(blk.ln2.bias),
                               dcol=None if blk.proj.bias is None else fl.grad(blk.proj.bias), want_bf16=amp,
@@ -523,13 +522,12 @@ class Gpt2Engine:
                      accumulate=True)
             d_qkv = buf("d_qkv", (M, 3 * C), act)
             ops.attn_bwd(s["qkv"].view(B, T, 3 * C), s["att"].view(B, T, C), d_att.view(B, T, C), s["lse"], H,
-                         scratch=scratch, dqkv=d_qkv.view(B, T, 3 * C))
+                         scratch=scratch, dqkv=d_qkv.view(B, T, 3 * C),
+                         dbias=None if blk.qkv.bias is None else fl.grad(blk.qkv.bias))
             d_ln1 = buf("d_ln", (M, C), act)
             ops.gemm(d_qkv, self._wb(blk.qkv.weight), b_layout=1, out=d_ln1)
             ops.gemm(d_qkv, s["ln1"], a_layout=1, b_layout=1, epilogue=EPI_ACCUM_F32, out=fl.grad(blk.qkv.weight),
                      accumulate=True)
-            if blk.qkv.bias is not None:
-                ops.colsum(d_qkv, fl.grad(blk.qkv.bias), accumulate=True, scratch=scratch)
             prev = pl.blocks[l - 1] if l > 0 else None
             ops.layernorm_bwd(d_ln1, x[l], blk.ln1.weight.data, s["m1"], s["r1"], add=dx,
                               dgamma=fl.grad(blk.ln1.weight), dbeta=None if blk.ln1.bias is None else fl.grad(blk.ln1.bias),

@@ -29,10 +29,12 @@ def _mat(t: torch.Tensor, name: str):
 
 
 def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=None, out2=None, aux=None,
-         tanh=False, accumulate=False, out_dtype=None, flags_extra=0):
+         tanh=False, accumulate=False, out_dtype=None, flags_extra=0, colsum_out=None, colsum_scratch=None):
     """D[M,N] = sum_k A(m,k) B(n,k) with a fused epilogue. a: [M,K] (layout 0) or [K,M] (layout 1); b likewise.
 
     bf16 operands -> tcgen05 kernel; fp32 operands -> FP32-pipe kernel. Returns out (and out2 for the GELU epilogue).
+    colsum_out (EPI_DGELU only): fp32 [N] vector that receives += the column sums of `out` (the bias gradient of the
+    Linear in front of the activation), produced by the same kernel on the bf16 path.
     """
     a, lda = _mat(a, "a")
     b, ldb = _mat(b, "b")
@@ -53,13 +55,17 @@ def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=Non
     ldo = out.stride(0)
     ldo2 = out2.stride(0) if out2 is not None else 0
     ldaux = aux.stride(0) if aux is not None else 0
+    if colsum_out is not None and epilogue != EPI_DGELU:
+        raise _lib.PenrozError("gemm: colsum_out goes with EPI_DGELU")
     if is_bf16:
         lib().gemm_bf16(ptr(a), lda, a_layout, ptr(b), ldb, b_layout, M, N, K, epilogue, ptr(bias), ptr(out), ldo,
-                        ptr(out2), ldo2, ptr(aux), ldaux, flags, stream())
+                        ptr(colsum_out) if colsum_out is not None else ptr(out2), ldo2, ptr(aux), ldaux, flags, stream())
     else:
         epi = EPI_STORE if epilogue == EPI_F32 else epilogue
         lib().gemm_f32(ptr(a), lda, a_layout, ptr(b), ldb, b_layout, M, N, K, epi, ptr(bias), ptr(out), ldo,
                        ptr(out2), ldo2, ptr(aux), ldaux, flags, stream())
+        if colsum_out is not None:
+            colsum(out, colsum_out, accumulate=True, scratch=colsum_scratch)
     return (out, out2) if epilogue == EPI_GELU else out
 
 
@@ -216,7 +222,9 @@ def attn_bwd_scratch_bytes(B, T, H, D, dtype) -> int:
     return lib().attn_bwd_scratch_bytes(B, T, H)
 
 
-def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None):
+def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None, dbias=None):
+    """dbias: fp32 [3C] vector that receives += the column sums of dqkv (the QKV bias gradient); the tensor-core kernels
+    produce it themselves, the fp32 path adds a column-sum pass."""
     B, T, C3 = qkv.shape
     D = (C3 // 3) // H
     if dqkv is None:
@@ -224,11 +232,14 @@ def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None):
     if scratch is None:
         scratch = torch.empty(attn_bwd_scratch_bytes(B, T, H, D, qkv.dtype), device=qkv.device, dtype=torch.uint8)
     if _use_tc_attention(qkv, D):
-        lib().attn_bwd_tc(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, ptr(scratch),
+        lib().attn_bwd_tc(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), ptr(dbias), B, T, H, D, ptr(scratch),
                           scratch.numel(), stream())
     else:
         lib().attn_bwd_simt(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, dt(qkv), ptr(scratch),
                             scratch.numel(), stream())
+        if dbias is not None:
+            ok = scratch.numel() >= lib().colsum_scratch_bytes(B * T, C3)
+            colsum(dqkv.view(B * T, C3), dbias, accumulate=True, scratch=scratch if ok else None)
     return dqkv
 
 

@@ -77,6 +77,11 @@ def test_gemm_bf16_epilogues(dev, bn_flag):
         d = ops.gemm(A, W, epilogue=ops.EPI_DGELU, aux=h, tanh=tanh, flags_extra=bn_flag)
         d_ref = (A.float() @ W.float().t()).bfloat16().float() * hh.grad
         assert rel_err(d, d_ref) < 6e-3
+        # the same with the bias-gradient side output: += column sums of the output as written
+        cs = torch.full((N,), 3.0, device=dev)
+        d2 = ops.gemm(A, W, epilogue=ops.EPI_DGELU, aux=h, tanh=tanh, flags_extra=bn_flag, colsum_out=cs)
+        assert torch.equal(d2, d)
+        assert rel_err(cs - 3.0, d.float().sum(0)) < 1e-5
     resid = torch.randn(M, N, device=dev)
     o = ops.gemm(A, W, epilogue=ops.EPI_RESID_F32, bias=bias, aux=resid, flags_extra=bn_flag)
     assert (o - (resid + pre_ref.float())).abs().max().item() < 0.05
@@ -222,10 +227,12 @@ def test_attention_simt(dev, B, T, H, D, dtype, monkeypatch):
     assert rel_err(lse, lse_ref) < 1e-5
     dout = torch.randn(B, T, C, device=dev).to(dtype)
     ref.backward(dout.float().view(B, T, H, D).transpose(1, 2))
-    dqkv = ops.attn_bwd(qkv, out, dout, lse, H)
+    db = torch.zeros(3 * C, device=dev)
+    dqkv = ops.attn_bwd(qkv, out, dout, lse, H, dbias=db)
     ref_d = torch.cat([t.grad.transpose(1, 2).reshape(B, T, C) for t in (q, k, v)], dim=2)
     btol = 2e-5 if dtype == torch.float32 else 1.5e-2
     assert rel_err(dqkv, ref_d) < btol
+    assert rel_err(db, dqkv.float().sum((0, 1))) < 1e-5
 
 
 @pytest.mark.parametrize("B,T,H", [(1, 128, 1), (2, 256, 3), (1, 200, 2), (2, 1024, 4), (1, 1000, 2)])
@@ -250,6 +257,11 @@ def test_attention_tensor_core(dev, B, T, H, monkeypatch):
     ref_d = torch.cat([t.grad.transpose(1, 2).reshape(B, T, C) for t in (q, k, v)], dim=2)
     for name, sl in (("dq", slice(0, C)), ("dk", slice(C, 2 * C)), ("dv", slice(2 * C, 3 * C))):
         assert rel_err(dqkv[..., sl], ref_d[..., sl]) < 2e-2, name
+    # the QKV bias gradient as a side output: += column sums of dqkv as written
+    db = torch.full((3 * C,), -2.0, device=dev)
+    dqkv2 = ops.attn_bwd(qkv, out, dout, lse, H, dbias=db)
+    assert rel_err(dqkv2, dqkv) < 1e-6   # dQ is reduced with floating-point atomics: not bit-stable run to run
+    assert rel_err(db + 2.0, dqkv2.float().sum((0, 1))) < 1e-5
 
 
 @pytest.mark.parametrize("mode", ["lazy", "classic"])
