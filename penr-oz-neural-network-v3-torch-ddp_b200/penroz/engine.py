@@ -468,13 +468,13 @@ class Gpt2Engine:
             # dW += dlogits^T . lnf (both operands MN-major; TMA zero-fills past column V of the padded chunk)
             ops.gemm(dl, lnf[r0:r1], a_layout=1, b_layout=1, epilogue=EPI_ACCUM_F32, out=g_head, accumulate=True)
             if pl.head.bias is not None:
-                ops.colsum(dl, fl.grad(pl.head.bias), accumulate=True, scratch=self._scratch(M, self._widest()))
+                ops.colsum(dl, fl.grad(pl.head.bias), accumulate=True, scratch=self._scratch(M, self._widest(), B, T))
         ops.ce_reduce(loss_rows, n_valid, loss)
         if cost_out is not None:
             ops.ce_reduce(loss_rows, n_valid, cost_out, out_scale=grad_scale, accumulate=not cost_first)
 
         # ---------------- backward through the blocks
-        scratch = self._scratch(M, self._widest())
+        scratch = self._scratch(M, self._widest(), B, T)
         dx_a, dx_b = buf("dx_a", (M, C), torch.float32), buf("dx_b", (M, C), torch.float32)
         dxb_a = buf("dxb_a", (M, C), torch.bfloat16) if amp else None
         dxb_b = buf("dxb_b", (M, C), torch.bfloat16) if amp else None
@@ -606,10 +606,11 @@ class Gpt2Engine:
         pl = self.plan
         return max(pl.vocab, max(b.fc.out_features for b in pl.blocks), 3 * pl.n_embd)
 
-    def _scratch(self, M, widest):
+    def _scratch(self, M, widest, B, T):
         C, H = self.plan.n_embd, self.plan.n_head
+        act = torch.bfloat16 if self.mode == "amp" else torch.float32
         need = max(ops.lib().layernorm_bwd_scratch_bytes(M, C), ops.lib().colsum_scratch_bytes(M, widest),
-                   M * H * 4 + M * C * 4 + 64)  # attention backward: row dot-products + fp32 dQ accumulator
+                   ops.attn_bwd_scratch_bytes(B, T, H, C // H, act) + 64)
         return self._buf("scratch", (int(need),), torch.uint8)
 
     # ------------------------------------------------------------------ optimizer
