@@ -22,6 +22,7 @@
 //     instead of waiting for its unlucky CTAs.
 #include "common.cuh"
 #include <stdlib.h>
+#include <string.h>
 
 namespace penroz {
 
@@ -860,6 +861,7 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const bool leader = (rank == 0);
     const uint32_t feed = bar_base + kFeedOffset;   // tile-feed ring; the leader's producer fills both CTAs' copies
 
+    pdl_trigger();   // the next kernel in the stream may begin its own setup as SMs free up
     unsigned int first_unit = 0;
     if (warp == 0 && lane == 0) {
         if (leader) first_unit = atomicAdd(&g_feed[p.feed_slot][0], 1u);
@@ -896,6 +898,11 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    // Programmatic dependent launch: this grid may have been started while its predecessor in the stream was still
+    // draining (its CTAs take SMs as the predecessor's leave them), so everything above -- barrier setup, TMEM
+    // allocation, descriptor prefetch -- overlapped that tail. Nothing of the predecessor's output is touched before
+    // this point; from here on its memory is complete and visible.
+    pdl_wait();
 
     const int units = p.tiles_m * p.tiles_n * p.splits;   // tiles_m counts 256-row tiles here
 
@@ -1197,7 +1204,15 @@ static int launch_gemm2_ew(const CUtensorMap& tmA, const CUtensorMap& tmB, const
         if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
         configured.fetch_or(1 << dev);
     }
-    kern<<<grid, Cfg2::kThreads, Cfg2::kSmemBytes, st>>>(tmA, tmB, om.o, om.o2, p);
+    static const bool pdl = !(getenv("PENROZ_GEMM_PDL") && !strcmp(getenv("PENROZ_GEMM_PDL"), "0"));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(Cfg2::kThreads); cfg.dynamicSmemBytes = Cfg2::kSmemBytes; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, kern, tmA, tmB, om.o, om.o2, p);
+    if (le != cudaSuccess) { set_error("gemm_bf16_tc2 launch: %s", cudaGetErrorString(le)); return PENROZ_ERR_CUDA; }
     count_launch();
     return check_launch("gemm_bf16_tc2");
 }
