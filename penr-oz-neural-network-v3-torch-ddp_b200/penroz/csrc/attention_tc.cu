@@ -450,57 +450,17 @@ __global__ void attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, const
     }
 }
 
-// dq_accum (fp32 [rows, C]) -> bf16 into the q third of dqkv [rows, 3C]. A thread keeps the same 4 columns over its
-// CTA's rows (blockIdx.x, + gridDim.x, ..., four rows in flight), so with dbias it also carries their column sums (of
-// the rounded values, as the bias gradient of the QKV Linear wants them) and adds them once at the end. The first CTAs
-// then fold the per-key-tile column sums of dK and dV the main kernel left in dkv_part [n_part][2][C].
-__global__ void __launch_bounds__(256)
-attn_bwd_dq_finish_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, size_t rows, int C,
-                          float* __restrict__ dbias, const float* __restrict__ dkv_part, int n_part) {
-    for (int c = threadIdx.x * 4; c < C; c += blockDim.x * 4) {
-        float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (size_t r0 = blockIdx.x; r0 < rows; r0 += 4 * (size_t)gridDim.x) {
-            float4 v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const size_t r = r0 + (size_t)u * gridDim.x;
-                v[u] = (r < rows) ? *reinterpret_cast<const float4*>(acc + r * C + c) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const size_t r = r0 + (size_t)u * gridDim.x;
-                if (r < rows) {
-                    uint2 w;
-                    w.x = pack_bf16x2(v[u].x, v[u].y);
-                    w.y = pack_bf16x2(v[u].z, v[u].w);
-                    *reinterpret_cast<uint2*>(dqkv + r * 3 * (size_t)C + c) = w;
-                    const float2 a = unpack_bf16x2(w.x), b = unpack_bf16x2(w.y);
-                    cs.x += a.x; cs.y += a.y; cs.z += b.x; cs.w += b.y;
-                }
-            }
-        }
-        if (dbias) {
-            atomicAdd(dbias + c, cs.x); atomicAdd(dbias + c + 1, cs.y);
-            atomicAdd(dbias + c + 2, cs.z); atomicAdd(dbias + c + 3, cs.w);
-        }
-    }
-    if (dbias && dkv_part) {
-        const int nsl = min((int)gridDim.x, 32);
-        if ((int)blockIdx.x < nsl) {
-            const int per = (n_part + nsl - 1) / nsl;
-            const int p0 = blockIdx.x * per, p1 = min(n_part, p0 + per);
-            for (int c = threadIdx.x * 4; c < 2 * C; c += blockDim.x * 4) {
-                float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int q = p0; q < p1; ++q) {
-                    const float4 v = *reinterpret_cast<const float4*>(dkv_part + (size_t)q * 2 * C + c);
-                    cs.x += v.x; cs.y += v.y; cs.z += v.z; cs.w += v.w;
-                }
-                if (p1 > p0) {
-                    atomicAdd(dbias + C + c, cs.x); atomicAdd(dbias + C + c + 1, cs.y);
-                    atomicAdd(dbias + C + c + 2, cs.z); atomicAdd(dbias + C + c + 3, cs.w);
-                }
-            }
-        }
+// dq_accum (fp32 [rows, C]) -> bf16 into the q third of dqkv [rows, 3C]
+__global__ void attn_bwd_dq_finish_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, size_t rows,
+                                          int C) {
+    const size_t n4 = rows * (size_t)C / 4;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = reinterpret_cast<const float4*>(acc)[i];
+        const size_t e = i * 4, r = e / C, c = e % C;
+        uint2 w;
+        w.x = pack_bf16x2(v.x, v.y);
+        w.y = pack_bf16x2(v.z, v.w);
+        *reinterpret_cast<uint2*>(dqkv + r * 3 * (size_t)C + c) = w;
     }
 }
 
@@ -525,8 +485,7 @@ __global__ void __launch_bounds__(576, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const __grid_constant__ CUtensorMap tmDQ,
                    const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
-                   __nv_bfloat16* __restrict__ dqkv, float* __restrict__ dkv_part, int Tn, int H, float scale,
-                   float scale_log2e) {
+                   __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
@@ -760,35 +719,17 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             __syncwarp();
             tmem_ld_32x16((which == 0 ? tDV : tDK) + lane_addr + part * 16, v);
             tmem_ld_wait();
-            uint32_t w[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) w[k] = pack_bf16x2(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
             if (key_ok) {
                 __nv_bfloat16* dst = which == 0 ? gv : gk;
-                *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
-                *reinterpret_cast<uint4*>(dst + 8) = make_uint4(w[4], w[5], w[6], w[7]);
-            }
-            if (dkv_part) {
-                // bias gradient of the QKV Linear: column sums of the rounded dK / dV over this warp's 32 keys go to
-                // shared memory (the P buffer: every MMA that read it has completed), where the four row quarters meet
-                float* bsum = reinterpret_cast<float*>(smem + AttnBwdSmem::kP) + (which * 4 + qd) * AT_D + part * 16;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    float2 c = key_ok ? unpack_bf16x2(w[k]) : make_float2(0.f, 0.f);
-                    c.x = warp_sum(c.x);
-                    c.y = warp_sum(c.y);
-                    if (lane == 0) { bsum[2 * k] = c.x; bsum[2 * k + 1] = c.y; }
+                for (int k = 0; k < 16; k += 8) {
+                    uint4 w;
+                    w.x = pack_bf16x2(__uint_as_float(v[k]), __uint_as_float(v[k + 1]));
+                    w.y = pack_bf16x2(__uint_as_float(v[k + 2]), __uint_as_float(v[k + 3]));
+                    w.z = pack_bf16x2(__uint_as_float(v[k + 4]), __uint_as_float(v[k + 5]));
+                    w.w = pack_bf16x2(__uint_as_float(v[k + 6]), __uint_as_float(v[k + 7]));
+                    *reinterpret_cast<uint4*>(dst + k) = w;
                 }
-            }
-        }
-        if (dkv_part) {
-            asm volatile("bar.sync 2, 512;" ::: "memory");   // the 16 softmax-gradient warps
-            if (threadIdx.x < 2 * AT_D) {
-                const int which = threadIdx.x / AT_D, d = threadIdx.x % AT_D;
-                const float* bs = reinterpret_cast<const float*>(smem + AttnBwdSmem::kP) + which * 4 * AT_D + d;
-                const float t = (bs[0] + bs[AT_D]) + (bs[2 * AT_D] + bs[3 * AT_D]);
-                // [key tile][K third, V third][C]; which 0 is dV
-                dkv_part[(((size_t)b * gridDim.x + jt) * 2 + (which == 0 ? 1 : 0)) * C + h * AT_D + d] = t;
             }
         }
         __syncwarp();
@@ -880,10 +821,14 @@ extern "C" int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B,
     return check_launch("attn_fwd_tc");
 }
 
+extern "C" int penroz_colsum(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype,
+                             void* scratch, size_t scratch_bytes, void* stream);
+extern "C" size_t penroz_colsum_scratch_bytes(int M, int N);
+
 extern "C" size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D) {
-    // row dot-products | fp32 dQ accumulator | per-key-tile column sums of dK, dV
-    return ((((size_t)B * H * T + 3) / 4) * 4 + (size_t)B * T * H * D + (size_t)B * ((T + AT_BN - 1) / AT_BN) * 2 * H * D) *
-           sizeof(float);
+    // row dot-products | fp32 dQ accumulator | partial column sums of the optional bias-gradient pass
+    return ((((size_t)B * H * T + 3) / 4) * 4 + (size_t)B * T * H * D) * sizeof(float) +
+           penroz_colsum_scratch_bytes(B * T, 3 * H * D);
 }
 
 // dqkv [B,T,3C] <- gradient of causal attention wrt the packed QKV buffer. scratch: delta [B,H,T] + dq accumulator
@@ -924,13 +869,20 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     attn_bwd_delta_kernel<<<(unsigned)((pairs * 8 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
-    float* dkv_part = dbias ? dq_acc + rows * C : nullptr;
-    attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, tmDQ, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, dkv_part, T, H, scale, scale * 1.44269504088896340736f);
-    {
-        const int threads = (C / 4 >= 256) ? 256 : ((C / 4 + 31) / 32 * 32);
-        size_t cap = (size_t)num_sms() * 8, want = (rows + 3) / 4;
-        attn_bwd_dq_finish_kernel<<<(unsigned)(want < cap ? want : cap), threads, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, C, dbias, dkv_part, (int)(grid.x * B));
-    }
+    attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, tmDQ, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
+    size_t n4 = rows * C / 4;
+    size_t g = (n4 + 255) / 256;
+    size_t cap = (size_t)num_sms() * 16;
+    attn_bwd_dq_finish_kernel<<<(unsigned)(g > cap ? cap : g), 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, C);
     count_launch(3);
-    return check_launch("attn_bwd_tc");
+    rc = check_launch("attn_bwd_tc");
+    if (rc == PENROZ_OK && dbias != nullptr) {
+        // bias gradient of the QKV Linear: one pass over dqkv (151 MB at 124M, ~28 us). Summing inside the kernels was
+        // tried and measured slower: dK/dV sums are cheap (per key tile, through shared memory) but dQ's need either an
+        // atomic per column from every CTA of the conversion pass (same-address atomics serialise in L2 at ~30 ns: +40 us)
+        // or so few CTAs that the pass loses its memory-level parallelism (+41 us in total)
+        float* cs = dq_acc + rows * C;
+        rc = penroz_colsum(dqkv, 3LL * C, (int)rows, 3 * C, dbias, 1, BF16, cs, penroz_colsum_scratch_bytes((int)rows, 3 * C), stream);
+    }
+    return rc;
 }
