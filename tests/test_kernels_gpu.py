@@ -157,6 +157,34 @@ def test_layernorm_fwd_bwd(dev, C):
     assert rel_err(dgam, gr.grad * 2) < 1e-2  # second accumulation used the bf16-rounded dy
 
 
+@pytest.mark.parametrize("rows,C", [(1001, 768), (7, 768), (1, 1024), (513, 100), (300, 2048), (4097, 1280)])
+@pytest.mark.parametrize("dy_dtype", [torch.float32, torch.bfloat16])
+def test_layernorm_bwd_shapes(dev, rows, C, dy_dtype):
+    """Odd row counts (a last stage with one row), one- and two-vector rows per thread (C <= 1024 / > 1024), a row
+    length the bulk copies cannot take (C % 8 != 0 -> the two-kernel form), with and without the residual gradient."""
+    from penroz import ops
+    torch.manual_seed(rows + C)
+    x = torch.randn(rows, C, device=dev) * 1.5 - 0.3
+    g = torch.randn(C, device=dev); b = torch.randn(C, device=dev)
+    _, mean, rstd = ops.layernorm_fwd(x, g, b, out_dtype=torch.float32)
+    dy = torch.randn(rows, C, device=dev).to(dy_dtype)
+    add = torch.randn(rows, C, device=dev)
+    xr = x.clone().requires_grad_(True); gr = g.clone().requires_grad_(True); br = b.clone().requires_grad_(True)
+    F.layer_norm(xr, (C,), gr, br, 1e-5).backward(dy.float())
+    for use_add in (True, False):
+        dgam = torch.zeros(C, device=dev); dbet = torch.zeros(C, device=dev); dcol = torch.zeros(C, device=dev)
+        want_bf16 = dy_dtype == torch.bfloat16
+        dx, dxb = ops.layernorm_bwd(dy, x, g, mean, rstd, add=add if use_add else None, dgamma=dgam, dbeta=dbet,
+                                    dcol=dcol, want_bf16=want_bf16)
+        ref_dx = xr.grad + (add if use_add else 0)
+        assert rel_err(dx, ref_dx) < 3e-5
+        assert rel_err(dgam, gr.grad) < 3e-5 and rel_err(dbet, br.grad) < 3e-5
+        seen = dx.bfloat16().float() if want_bf16 else dx
+        assert rel_err(dcol, seen.sum(0)) < 1e-4
+        if want_bf16:
+            assert torch.equal(dxb, dx.bfloat16())
+
+
 def test_embedding(dev):
     from penroz import ops
     torch.manual_seed(3)
