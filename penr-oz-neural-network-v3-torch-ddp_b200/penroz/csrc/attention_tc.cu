@@ -44,8 +44,12 @@ __device__ __forceinline__ uint32_t sw128_off(int row, int col) {
 // cycles of issue each -> S complete -> softmax wakes). The SFU is busy 66 % of the time: the two CTAs fall into
 // lock-step (they share the SFU fairly, finish their passes together and idle through the chain together). Packing two
 // exponentials per SFU operation (ex2.approx.f16x2) measured SLOWER (171 vs 153 us: the packed form is not double
-// rate and adds conversions). What is left is the two-tile ping-pong inside one CTA (explicitly alternating softmax
-// groups) and an FMA-pipe polynomial for part of the exponentials.
+// rate and adds conversions), and moving a quarter of the exponentials to the FMA pipe (degree-3 polynomial on packed
+// fp32 pairs, exponent added as an integer) left the kernel at 151 us: the pass has a second bound of the same size,
+// the 64 B/clk at which tensor memory is read (a 128x128 fp32 S tile is 64 KB = 1,024 cycles per CTA, 2,048 for the two
+// resident CTAs). What is left is taking the ~1,000-cycle hand-off chain off the critical path: S_{j+1} computed while
+// softmax_j runs needs a second S buffer, which two 256-column CTAs per SM do not have (S 128 + P 64 + O 64) -- i.e. one
+// 512-column CTA per SM working on two query tiles with explicitly alternating softmax groups.
 struct AttnFwdSmem {
     // sized so that TWO CTAs fit in one SM's 227 KB (one CTA's softmax overlaps the other's MMAs): K is single
     // buffered (its only reader, the S MMA, retires long before the next K is needed), V double buffered
