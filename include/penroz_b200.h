@@ -47,6 +47,11 @@ extern "C" {
                                    vector that receives += the column sums of out (bias gradient of the Linear in
                                    front of the activation)                                 */
 #define PENROZ_EPI_F32 6        /* out(f32) = acc + bias                                   */
+#define PENROZ_EPI_STORE_ROWDOT 7 /* penroz_gemm_bf16, shapes of the CTA-pair kernel (M >= 256, N > 128, N % 64 == 0):
+                                   out = bf16(acc + bias) and, for every 64-column group g of row r,
+                                   out2(f32)[((r / T)·(N/64) + g)·T + r % T] = sum_c out[r,64g+c]·aux[r,64g+c]
+                                   with T = ldo2 rows per sequence: the attention backward's delta, produced by the
+                                   GEMM that computes dO (aux = the attention output)          */
 /* flags: bit0 tanh-GELU (else erf), bit1 accumulate into out, bit2 force 128-wide tile, bit3 force 256-wide tile */
 
 /* ---- library ---- */
@@ -149,11 +154,13 @@ int penroz_attn_bwd_simt(const void* qkv, const void* out, const void* dout, con
  * q, k, v and dO tiles fetched from the packed buffers by TMA. Replaces the same reference lines as above for the
  * bf16-autocast training step. The backward needs scratch (row dot-products + an fp32 dQ accumulator it zeroes).
  * dbias (optional, fp32 [3C]) receives += the column sums of dqkv as written (bf16): the bias gradient of the QKV Linear
- * (nn.Linear backward, mappers.py:156), summed where dK, dV and dQ leave the kernels instead of by a pass over dqkv. */
+ * (nn.Linear backward, mappers.py:156). flags bit 0: the row dot-products delta[b,h,t] = sum_d dO·O are already at the
+ * head of scratch (B·H·T floats) -- written by the GEMM that produced dout (PENROZ_EPI_STORE_ROWDOT) -- and the pass that
+ * would compute them is skipped. */
 int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
 size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D);
 int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* dbias,
-                       int B, int T, int H, int D, void* scratch, size_t scratch_bytes, void* stream);
+                       int flags, int B, int T, int H, int D, void* scratch, size_t scratch_bytes, void* stream);
 
 /* ---- softmax cross-entropy over a chunk of logits rows ----
  * Replaces F.cross_entropy(logits.view(-1,V), target.view(-1)) (neural_net_model.py:264-267): mean over rows whose

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libpenroz_b200.so")
 HEADER_PATH = os.path.normpath(os.path.join(_HERE, "..", "..", "include", "penroz_b200.h"))
 
 F32, BF16 = 0, 1
-EPI_STORE, EPI_GELU, EPI_RESID_F32, EPI_RESID_BF16, EPI_ACCUM_F32, EPI_DGELU, EPI_F32 = range(7)
+EPI_STORE, EPI_GELU, EPI_RESID_F32, EPI_RESID_BF16, EPI_ACCUM_F32, EPI_DGELU, EPI_F32, EPI_ROWDOT = range(8)
 FLAG_TANH, FLAG_ACCUM, FLAG_BN128, FLAG_BN256 = 1, 2, 4, 8
 
 _SCALARS = {

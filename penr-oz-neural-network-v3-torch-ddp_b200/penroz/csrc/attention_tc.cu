@@ -838,8 +838,8 @@ extern "C" size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D) {
 // dqkv [B,T,3C] <- gradient of causal attention wrt the packed QKV buffer. scratch: delta [B,H,T] + dq accumulator
 // [B*T, C] fp32 (zeroed here with cudaMemsetAsync on `stream`).
 extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
-                                  float* dbias, int B, int T, int H, int D, void* scratch, size_t scratch_bytes,
-                                  void* stream) {
+                                  float* dbias, int flags, int B, int T, int H, int D, void* scratch,
+                                  size_t scratch_bytes, void* stream) {
     PENROZ_REQUIRE(B > 0 && T > 0 && H > 0, "attn_bwd_tc: bad shape");
     PENROZ_REQUIRE(D == 64, "attn_bwd_tc: head_dim %d unsupported (tensor-core path is head_dim 64)", D);
     PENROZ_REQUIRE(B <= 65535 && H <= 65535, "attn_bwd_tc: B/H too large for the launch grid");
@@ -870,7 +870,8 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     cudaError_t e = cudaMemsetAsync(dq_acc, 0, rows * C * sizeof(float), st);
     if (e != cudaSuccess) { set_error("attn_bwd_tc: memset: %s", cudaGetErrorString(e)); return PENROZ_ERR_CUDA; }
     const long long pairs = (long long)rows * H;
-    attn_bwd_delta_kernel<<<(unsigned)((pairs * 8 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
+    if (!(flags & 1))   // bit 0: the caller's projection-gradient GEMM already left delta at the head of scratch
+        attn_bwd_delta_kernel<<<(unsigned)((pairs * 8 + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, (int)rows, T, H);
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
     attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, tmDQ, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);

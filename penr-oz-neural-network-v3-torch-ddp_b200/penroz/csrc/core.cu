@@ -44,7 +44,7 @@ extern "C" const char* penroz_last_error(void) { return tl_error; }
 
 extern "C" unsigned long long penroz_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
-extern "C" int penroz_abi_version(void) { return 3; }
+extern "C" int penroz_abi_version(void) { return 4; }
 
 // Refuses anything but a compute-capability 10.x device: the kernels are sm_100a-only SASS.
 extern "C" int penroz_query(int* cc_major, int* cc_minor, int* sm_count) {

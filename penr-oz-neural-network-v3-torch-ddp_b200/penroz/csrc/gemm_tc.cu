@@ -38,6 +38,7 @@ enum Epi {
     EPI_ACCUM_F32 = 4,   // out(f32) (+)= acc        (beta flag; split-K uses red.add)
     EPI_DGELU = 5,       // out = bf16(float(bf16(acc)) * gelu'(aux bf16))
     EPI_F32 = 6,         // out(f32) = acc + bias
+    EPI_ROWDOT = 7,      // out = bf16(acc + bias); out2(f32)[(r / T) * (N/64) + g][r % T] = sum_c out[r,64g+c] * aux[r,64g+c]
 };
 
 struct GemmParams {
@@ -54,6 +55,7 @@ struct GemmParams {
     int gelu_tanh;
     int beta;
     int feed_slot;   // which g_feed counter pair this launch draws its work units from
+    int seq;         // EPI_ROWDOT: rows per sequence (T)
 };
 
 // ------------------------------------------------------------------ dynamic tile feed
@@ -376,7 +378,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float (&acc)
 // (ncu: 120.8 M warp instructions against 26.5 M for the plain kernel, 201 us against ~125 us of mainloop).
 template <int EPI> struct EpiTraits {
     static constexpr bool kF32Out = (EPI == EPI_RESID_F32 || EPI == EPI_ACCUM_F32 || EPI == EPI_F32);
-    static constexpr bool kHasAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16);
+    static constexpr bool kHasAux = (EPI == EPI_RESID_F32 || EPI == EPI_DGELU || EPI == EPI_RESID_BF16 || EPI == EPI_ROWDOT);
     static constexpr bool kAuxF32 = (EPI == EPI_RESID_F32);
     static constexpr int kBoxBytes = kF32Out ? 4096 : 2048;
 };
@@ -434,9 +436,11 @@ __device__ __forceinline__ void box_send(const void* tmap, uint32_t box, int lan
 //   EPI_RESID_F32  fp32 box (SWIZZLE_128B): box += bf16(acc + bias)
 //   EPI_RESID_BF16 bf16 box (SWIZZLE_64B):  box = bf16(box + bf16(acc + bias))
 //   EPI_DGELU      bf16 box:                box = bf16(bf16(acc) * gelu'(box))
+//   EPI_ROWDOT     bf16 box:                returns sum_c bf16(acc + bias)[c] * box[c], then box = bf16(acc + bias)
 template <int EPI>
-__device__ __forceinline__ void epilogue_chunk_box(const GemmParams& p, const uint32_t (&v)[32], uint32_t box, int lane,
-                                                   int col0) {
+__device__ __forceinline__ float epilogue_chunk_box(const GemmParams& p, const uint32_t (&v)[32], uint32_t box, int lane,
+                                                    int col0) {
+    float dot = 0.f;
     float acc[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
@@ -482,6 +486,16 @@ __device__ __forceinline__ void epilogue_chunk_box(const GemmParams& p, const ui
                 const float2 a = unpack_bf16x2(h[i]);
                 w[i] = pack_bf16x2(a.x + bf16_round(acc[2 * i]), a.y + bf16_round(acc[2 * i + 1]));
             }
+        } else if (EPI == EPI_ROWDOT) {
+            float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                w[i] = pack_bf16x2(acc[2 * i], acc[2 * i + 1]);
+                const float2 a = unpack_bf16x2(h[i]), r = unpack_bf16x2(w[i]);
+                d0 = fmaf(r.x, a.x, d0);
+                d1 = fmaf(r.y, a.y, d1);
+            }
+            dot = d0 + d1;
         } else if (p.gelu_tanh) {   // warp-uniform choice outside the element loop: straight-line code per element
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
@@ -515,6 +529,7 @@ __device__ __forceinline__ void epilogue_chunk_box(const GemmParams& p, const ui
             if (col0 + lane < p.N) atomicAdd(reinterpret_cast<float*>(p.out2) + col0 + lane, cs);
         }
     }
+    return dot;
 }
 
 // Epilogues without an aux operand (EPI_BF16, EPI_GELU, EPI_F32, EPI_ACCUM_F32): registers -> box -> store
@@ -1036,6 +1051,7 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     tma_load_2d(stg + (uint32_t)((cc & 1) * Cfg::kBoxBytes), &tmO2, bar, c_first + cc * 32, row0);
                 };
                 const bool live = row0 < p.M;
+                float rowdot = 0.f;
                 if (lane == 0 && live) {
                     if (c_first < p.N) load_box(0);
                     if (c_first + 32 < p.N) load_box(1);
@@ -1057,7 +1073,17 @@ gemm_bf16_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     const uint32_t box = stg + (uint32_t)((cc & 1) * Cfg::kBoxBytes);
                     mbar_wait(aux_bar + 8u * (cc & 1), (aux_ph >> (cc & 1)) & 1u);
                     aux_ph ^= 1u << (cc & 1);
-                    epilogue_chunk_box<EPI>(p, v, box, lane, col0);
+                    const float dot = epilogue_chunk_box<EPI>(p, v, box, lane, col0);
+                    if (EPI == EPI_ROWDOT) {
+                        // two chunks make a 64-column group (a head): the row's dot product goes to [sequence][group][t]
+                        if ((cc & 1) == 0) {
+                            rowdot = dot;
+                        } else if (row0 + lane < p.M) {
+                            const int row = row0 + lane, g = col0 >> 6;
+                            reinterpret_cast<float*>(p.out2)[((size_t)(row / p.seq) * (p.N >> 6) + g) * p.seq + row % p.seq] =
+                                rowdot + dot;
+                        }
+                    }
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
@@ -1231,6 +1257,7 @@ static int dispatch_epi2(int epi, const CUtensorMap& a, const CUtensorMap& b, co
         case EPI_ACCUM_F32: return launch_gemm2<EPI_ACCUM_F32>(a, b, om, p, grid, st);
         case EPI_DGELU: return launch_gemm2<EPI_DGELU>(a, b, om, p, grid, st);
         case EPI_F32: return launch_gemm2<EPI_F32>(a, b, om, p, grid, st);
+        case EPI_ROWDOT: return launch_gemm2<EPI_ROWDOT>(a, b, om, p, grid, st);
     }
     set_error("gemm_bf16: unknown epilogue %d", epi);
     return PENROZ_ERR_ARG;
@@ -1263,9 +1290,12 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     PENROZ_REQUIRE(A && B && out, "gemm_bf16: null operand");
     PENROZ_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_bf16: lda/ldb must be multiples of 8 elements (16 B) for TMA");
     PENROZ_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0), "gemm_bf16: operands must be 16-byte aligned");
-    PENROZ_REQUIRE(epilogue >= 0 && epilogue <= EPI_F32, "gemm_bf16: bad epilogue %d", epilogue);
+    PENROZ_REQUIRE(epilogue >= 0 && epilogue <= EPI_ROWDOT, "gemm_bf16: bad epilogue %d", epilogue);
+    if (epilogue == EPI_ROWDOT)
+        PENROZ_REQUIRE(out2 != nullptr && ldo2 > 0 && N % 64 == 0 && M % ldo2 == 0,
+                       "gemm_bf16: row-dot epilogue needs out2, rows per sequence in ldo2 (dividing M=%d) and N=%d %% 64 == 0", M, N);
     if (epilogue == EPI_GELU) PENROZ_REQUIRE(out2 != nullptr, "gemm_bf16: GELU epilogue needs out2");
-    if (epilogue == EPI_RESID_F32 || epilogue == EPI_RESID_BF16 || epilogue == EPI_DGELU)
+    if (epilogue == EPI_RESID_F32 || epilogue == EPI_RESID_BF16 || epilogue == EPI_DGELU || epilogue == EPI_ROWDOT)
         PENROZ_REQUIRE(aux != nullptr, "gemm_bf16: epilogue %d needs aux", epilogue);
     cudaStream_t st = (cudaStream_t)stream;
 
@@ -1277,6 +1307,7 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     p.out = out; p.ldo = ldo; p.out2 = out2; p.ldo2 = ldo2; p.aux = aux; p.ldaux = ldaux;
     p.gelu_tanh = (flags & 1) ? 1 : 0;
     p.beta = (flags & 2) ? 1 : 0;
+    p.seq = (epilogue == EPI_ROWDOT) ? (int)ldo2 : 1;
     static std::atomic<unsigned int> feed_seq{0};
     p.feed_slot = (int)(feed_seq.fetch_add(1, std::memory_order_relaxed) % kFeedCounters);
 
@@ -1295,7 +1326,7 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     const bool tma_out_ok = ((uintptr_t)out % 16 == 0) && ((size_t)ldo * oesz % 16 == 0) &&
                             (epilogue != EPI_GELU || (((uintptr_t)out2 % 16 == 0) && ((size_t)ldo2 * 2 % 16 == 0))) &&
                             (epilogue != EPI_RESID_F32 || (((uintptr_t)aux % 16 == 0) && ((size_t)ldaux * 4 % 16 == 0))) &&
-                            ((epilogue != EPI_RESID_BF16 && epilogue != EPI_DGELU) ||
+                            ((epilogue != EPI_RESID_BF16 && epilogue != EPI_DGELU && epilogue != EPI_ROWDOT) ||
                              (((uintptr_t)aux % 16 == 0) && ((size_t)ldaux * 2 % 16 == 0)));
     const bool pair_ok = (M >= 256) && (N > 128) && (sms >= 2) && !(flags & 16) && tma_out_ok;
     const double c_pair = pair_ok ? (double)ceil_div(u_pair, sms / 2) * 1.0 : 1e30;
@@ -1313,6 +1344,10 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
     }
     if (flags & 4) { bn = 128; pair = false; }
     if (flags & 8) { bn = 256; pair = pair_ok; }
+    if (epilogue == EPI_ROWDOT) {   // exists in the CTA-pair kernel only
+        PENROZ_REQUIRE(pair_ok, "gemm_bf16: the row-dot epilogue needs M >= 256, N > 128 and 16-byte aligned out / aux rows");
+        bn = 256; pair = true;
+    }
     // a single 128-row tile of activations (decode at batch <= 128): the kernel is a weight stream and every CTA pulls
     // BN rows of W, so narrower tiles = more CTAs pulling in parallel
     if (!(flags & 12) && M <= 128 && epilogue != EPI_ACCUM_F32 && N > 64 && ceil_div(N, 128) * 2 <= sms) { bn = 64; pair = false; }
@@ -1363,7 +1398,7 @@ extern "C" int penroz_gemm_bf16(const void* A, long long lda, int a_layout, cons
         if (epilogue == EPI_GELU) {
             rc = encode_out_2d(&om.o2, out2, false, (uint64_t)N, (uint64_t)M, (uint64_t)ldo2);
             if (rc) return rc;
-        } else if (epilogue == EPI_RESID_F32 || epilogue == EPI_RESID_BF16 || epilogue == EPI_DGELU) {
+        } else if (epilogue == EPI_RESID_F32 || epilogue == EPI_RESID_BF16 || epilogue == EPI_DGELU || epilogue == EPI_ROWDOT) {
             // the aux operand, loaded box by box
             rc = encode_out_2d(&om.o2, aux, epilogue == EPI_RESID_F32, (uint64_t)N, (uint64_t)M, (uint64_t)ldaux);
             if (rc) return rc;

@@ -517,13 +517,21 @@ class Gpt2Engine:
             dy = dxb if amp else dx
             # ---- attention branch
             d_att = buf("d_att", (M, C), act)
-            ops.gemm(dy, self._wb(blk.proj.weight), b_layout=1, out=d_att)
+            # the GEMM that produces dO also leaves delta = rowsum(dO * O) per head at the head of the scratch buffer,
+            # where the attention backward looks for it (nothing else touches scratch in between)
+            fuse_delta = (ops.rowdot_fusable(M, C, C // H, act) and ops._use_tc_attention(s["qkv"], C // H)
+                          and os.environ.get("PENROZ_FUSE_DELTA", "1") != "0")
+            if fuse_delta:
+                ops.gemm(dy, self._wb(blk.proj.weight), b_layout=1, out=d_att, epilogue=ops.EPI_ROWDOT, aux=s["att"],
+                         rowdot_out=scratch, seq_len=T)
+            else:
+                ops.gemm(dy, self._wb(blk.proj.weight), b_layout=1, out=d_att)
             ops.gemm(dy, s["att"], a_layout=1, b_layout=1, epilogue=EPI_ACCUM_F32, out=fl.grad(blk.proj.weight),
                      accumulate=True)
             d_qkv = buf("d_qkv", (M, 3 * C), act)
             ops.attn_bwd(s["qkv"].view(B, T, 3 * C), s["att"].view(B, T, C), d_att.view(B, T, C), s["lse"], H,
                          scratch=scratch, dqkv=d_qkv.view(B, T, 3 * C),
-                         dbias=None if blk.qkv.bias is None else fl.grad(blk.qkv.bias))
+                         dbias=None if blk.qkv.bias is None else fl.grad(blk.qkv.bias), delta_ready=fuse_delta)
             d_ln1 = buf("d_ln", (M, C), act)
             ops.gemm(d_qkv, self._wb(blk.qkv.weight), b_layout=1, out=d_ln1)
             ops.gemm(d_qkv, s["ln1"], a_layout=1, b_layout=1, epilogue=EPI_ACCUM_F32, out=fl.grad(blk.qkv.weight),

@@ -9,7 +9,7 @@ import os
 import torch
 
 from . import _lib
-from ._lib import (BF16, EPI_ACCUM_F32, EPI_DGELU, EPI_F32, EPI_GELU, EPI_RESID_BF16, EPI_RESID_F32, EPI_STORE, F32,
+from ._lib import (BF16, EPI_ACCUM_F32, EPI_DGELU, EPI_F32, EPI_GELU, EPI_RESID_BF16, EPI_RESID_F32, EPI_ROWDOT, EPI_STORE, F32,
                    FLAG_ACCUM, FLAG_TANH, dt, lib, ptr, stream)
 
 
@@ -29,12 +29,15 @@ def _mat(t: torch.Tensor, name: str):
 
 
 def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=None, out2=None, aux=None,
-         tanh=False, accumulate=False, out_dtype=None, flags_extra=0, colsum_out=None, colsum_scratch=None):
+         tanh=False, accumulate=False, out_dtype=None, flags_extra=0, colsum_out=None, colsum_scratch=None,
+         rowdot_out=None, seq_len=0):
     """D[M,N] = sum_k A(m,k) B(n,k) with a fused epilogue. a: [M,K] (layout 0) or [K,M] (layout 1); b likewise.
 
     bf16 operands -> tcgen05 kernel; fp32 operands -> FP32-pipe kernel. Returns out (and out2 for the GELU epilogue).
     colsum_out (EPI_DGELU only): fp32 [N] vector that receives += the column sums of `out` (the bias gradient of the
     Linear in front of the activation), produced by the same kernel on the bf16 path.
+    rowdot_out / seq_len (EPI_ROWDOT only, bf16 shapes of the CTA-pair kernel): fp32 buffer that receives, per row and
+    64-column group, the dot product of the output row with the aux row, laid out [M / seq_len][N / 64][seq_len].
     """
     a, lda = _mat(a, "a")
     b, ldb = _mat(b, "b")
@@ -54,6 +57,10 @@ def gemm(a, b, *, a_layout=0, b_layout=0, epilogue=EPI_STORE, bias=None, out=Non
     flags = (FLAG_TANH if tanh else 0) | (FLAG_ACCUM if accumulate else 0) | flags_extra
     ldo = out.stride(0)
     ldo2 = out2.stride(0) if out2 is not None else 0
+    if epilogue == EPI_ROWDOT:
+        if rowdot_out is None or seq_len <= 0 or not is_bf16:
+            raise _lib.PenrozError("gemm: EPI_ROWDOT needs bf16 operands, rowdot_out and seq_len")
+        out2, ldo2 = rowdot_out, int(seq_len)
     ldaux = aux.stride(0) if aux is not None else 0
     if colsum_out is not None and epilogue != EPI_DGELU:
         raise _lib.PenrozError("gemm: colsum_out goes with EPI_DGELU")
@@ -222,7 +229,12 @@ def attn_bwd_scratch_bytes(B, T, H, D, dtype) -> int:
     return lib().attn_bwd_scratch_bytes(B, T, H)
 
 
-def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None, dbias=None):
+def rowdot_fusable(M, N, D, dtype) -> bool:
+    """Can the GEMM that produces dO also produce the attention backward's row dot-products (EPI_ROWDOT)?"""
+    return dtype == torch.bfloat16 and D == 64 and M >= 256 and N > 128 and N % 64 == 0
+
+
+def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None, dbias=None, delta_ready=False):
     """dbias: fp32 [3C] vector that receives += the column sums of dqkv (the QKV bias gradient); the tensor-core kernels
     produce it themselves, the fp32 path adds a column-sum pass."""
     B, T, C3 = qkv.shape
@@ -232,8 +244,8 @@ def attn_bwd(qkv, out, dout, lse, H, scratch=None, dqkv=None, dbias=None):
     if scratch is None:
         scratch = torch.empty(attn_bwd_scratch_bytes(B, T, H, D, qkv.dtype), device=qkv.device, dtype=torch.uint8)
     if _use_tc_attention(qkv, D):
-        lib().attn_bwd_tc(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), ptr(dbias), B, T, H, D, ptr(scratch),
-                          scratch.numel(), stream())
+        lib().attn_bwd_tc(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), ptr(dbias), 1 if delta_ready else 0,
+                          B, T, H, D, ptr(scratch), scratch.numel(), stream())
     else:
         lib().attn_bwd_simt(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), B, T, H, D, dt(qkv), ptr(scratch),
                             scratch.numel(), stream())

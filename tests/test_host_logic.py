@@ -23,7 +23,7 @@ def test_c_abi_library_loads_and_exports_every_declared_symbol():
     lib = _lib.lib()                        # dlopen works without a GPU
     for name in protos:
         assert hasattr(lib._cdll, name), f"{name} declared in include/penroz_b200.h but not exported"
-    assert lib.abi_version() == 3 and lib.kv_page_size() == 64
+    assert lib.abi_version() == 4 and lib.kv_page_size() == 64
     assert lib.layernorm_bwd_scratch_bytes(32768, 768) > 0
     if not torch.cuda.is_available():
         with pytest.raises(_lib.PenrozError):

@@ -100,6 +100,28 @@ def test_gemm_bf16_epilogues(dev, bn_flag):
     assert rel_err(g0, 2 * ref) < 2e-5
 
 
+def test_gemm_rowdot_epilogue_feeds_attention_backward(dev):
+    """EPI_ROWDOT: the GEMM that produces dO also leaves delta[b,h,t] = sum_d dO*O where the attention backward reads it."""
+    from penroz import ops
+    torch.manual_seed(11)
+    B, T, H, D = 2, 256, 4, 64
+    C, M = H * D, B * T
+    dy = torch.randn(M, C, device=dev).bfloat16()
+    W = (torch.randn(C, C, device=dev) * 0.05).bfloat16()          # [N_out, K_in] as stored: dO = dy . W (MN-major B)
+    qkv = torch.randn(B, T, 3 * C, device=dev).bfloat16()
+    O, lse = ops.attn_fwd(qkv, H)
+    scratch = torch.zeros(ops.attn_bwd_scratch_bytes(B, T, H, D, qkv.dtype), device=dev, dtype=torch.uint8)
+    dO_plain = ops.gemm(dy, W, b_layout=1)
+    dO = ops.gemm(dy, W, b_layout=1, epilogue=ops.EPI_ROWDOT, aux=O.view(M, C), rowdot_out=scratch, seq_len=T)
+    assert torch.equal(dO, dO_plain)
+    delta = scratch[: B * H * T * 4].view(torch.float32).view(B, H, T)
+    ref = (dO.float() * O.view(M, C).float()).view(B, T, H, D).sum(-1).permute(0, 2, 1)
+    assert rel_err(delta, ref) < 1e-5
+    d1 = ops.attn_bwd(qkv, O, dO.view(B, T, C), lse, H, scratch=scratch, delta_ready=True)
+    d2 = ops.attn_bwd(qkv, O, dO.view(B, T, C), lse, H)
+    assert rel_err(d1, d2) < 2e-3    # dQ is reduced with floating-point atomics; delta differs by summation order only
+
+
 def test_gemm_f32(dev):
     from penroz import ops
     torch.manual_seed(1)
