@@ -468,6 +468,83 @@ __global__ void attn_bwd_dq_finish_kernel(const float* __restrict__ acc, __nv_bf
     }
 }
 
+// The same conversion fused with the QKV bias gradient: one pass over the three thirds of dqkv that converts the Q
+// third from the fp32 accumulator on the way and leaves per-slab column sums of the bf16 values (Q as just rounded,
+// K and V as the main kernel wrote them) in part[gridDim.y][3C]; attn_bwd_bias_reduce_kernel folds the slabs in fixed
+// order. Replaces the conversion pass plus a column-sum pass over dqkv (250 MB instead of 300 MB, two launches fewer).
+// A thread owns 8 columns (32 lanes x 8 = 256 columns per CTA), 8 row lanes, four rows in flight.
+__global__ void __launch_bounds__(256)
+attn_bwd_finish_colsum_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int rows, int C,
+                              float* __restrict__ part) {
+    __shared__ float sm[8][32][9];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int col = (blockIdx.x * 32 + tx) * 8;
+    const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
+    const int r0 = blockIdx.y * rows_per, r1 = min(rows, r0 + rows_per);
+    float s[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k] = 0.f;
+    if (col < 3 * C) {
+        const bool is_q = col < C;
+        for (int r = r0 + ty; r < r1; r += 32) {
+            uint4 w[4];
+            if (is_q) {
+                float4 a[4][2];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int rr = r + 8 * u;
+                    if (rr < r1) {
+                        a[u][0] = *reinterpret_cast<const float4*>(acc + (size_t)rr * C + col);
+                        a[u][1] = *reinterpret_cast<const float4*>(acc + (size_t)rr * C + col + 4);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int rr = r + 8 * u;
+                    if (rr < r1) {
+                        w[u] = make_uint4(pack_bf16x2(a[u][0].x, a[u][0].y), pack_bf16x2(a[u][0].z, a[u][0].w),
+                                          pack_bf16x2(a[u][1].x, a[u][1].y), pack_bf16x2(a[u][1].z, a[u][1].w));
+                        *reinterpret_cast<uint4*>(dqkv + (size_t)rr * 3 * C + col) = w[u];
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int rr = r + 8 * u;
+                    if (rr < r1) w[u] = *reinterpret_cast<const uint4*>(dqkv + (size_t)rr * 3 * C + col);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (r + 8 * u < r1) {
+                    const float2 p0 = unpack_bf16x2(w[u].x), p1 = unpack_bf16x2(w[u].y), p2 = unpack_bf16x2(w[u].z), p3 = unpack_bf16x2(w[u].w);
+                    s[0] += p0.x; s[1] += p0.y; s[2] += p1.x; s[3] += p1.y;
+                    s[4] += p2.x; s[5] += p2.y; s[6] += p3.x; s[7] += p3.y;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sm[ty][tx][k] = s[k];
+    __syncthreads();
+    if (ty == 0 && col < 3 * C) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float t = 0.f;
+#pragma unroll
+            for (int w8 = 0; w8 < 8; ++w8) t += sm[w8][tx][k];
+            part[(size_t)blockIdx.y * 3 * C + col + k] = t;
+        }
+    }
+}
+__global__ void attn_bwd_bias_reduce_kernel(const float* __restrict__ part, int nparts, int N, float* __restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= N) return;
+    float t = 0.f;
+    for (int q = 0; q < nparts; ++q) t += part[(size_t)q * N + c];
+    out[c] += t;
+}
+
 struct AttnBwdSmem {
     static constexpr int kK = 0;                       // 16 KB   K_j  [128 keys][64]
     static constexpr int kV = 16384;                   // 16 KB   V_j
@@ -825,8 +902,6 @@ extern "C" int penroz_attn_fwd_tc(const void* qkv, void* out, float* lse, int B,
     return check_launch("attn_fwd_tc");
 }
 
-extern "C" int penroz_colsum(const void* X, long long ld, int M, int N, float* out, int accumulate, int dtype,
-                             void* scratch, size_t scratch_bytes, void* stream);
 extern "C" size_t penroz_colsum_scratch_bytes(int M, int N);
 
 extern "C" size_t penroz_attn_bwd_tc_scratch_bytes(int B, int T, int H, int D) {
@@ -875,19 +950,21 @@ extern "C" int penroz_attn_bwd_tc(const void* qkv, const void* out, const void* 
     dim3 grid((T + AT_BN - 1) / AT_BN, H, B);
     const float scale = 1.0f / sqrtf((float)D);
     attn_bwd_tc_kernel<<<grid, 576, AttnBwdSmem::kBytes, st>>>(tmQ, tmG, tmDQ, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, T, H, scale, scale * 1.44269504088896340736f);
-    size_t n4 = rows * C / 4;
-    size_t g = (n4 + 255) / 256;
-    size_t cap = (size_t)num_sms() * 16;
-    attn_bwd_dq_finish_kernel<<<(unsigned)(g > cap ? cap : g), 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, C);
-    count_launch(3);
-    rc = check_launch("attn_bwd_tc");
-    if (rc == PENROZ_OK && dbias != nullptr) {
-        // bias gradient of the QKV Linear: one pass over dqkv (151 MB at 124M, ~28 us). Summing inside the kernels was
-        // tried and measured slower: dK/dV sums are cheap (per key tile, through shared memory) but dQ's need either an
-        // atomic per column from every CTA of the conversion pass (same-address atomics serialise in L2 at ~30 ns: +40 us)
-        // or so few CTAs that the pass loses its memory-level parallelism (+41 us in total)
-        float* cs = dq_acc + rows * C;
-        rc = penroz_colsum(dqkv, 3LL * C, (int)rows, 3 * C, dbias, 1, BF16, cs, penroz_colsum_scratch_bytes((int)rows, 3 * C), stream);
+    if (dbias != nullptr) {
+        // dQ conversion and the bias gradient of the QKV Linear (column sums of dqkv as written) in one pass
+        constexpr int kParts = 32;
+        float* part = dq_acc + rows * C;
+        dim3 g((3 * C + 255) / 256, kParts);
+        attn_bwd_finish_colsum_kernel<<<g, 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, (int)rows, C, part);
+        attn_bwd_bias_reduce_kernel<<<(3 * C + 255) / 256, 256, 0, st>>>(part, kParts, 3 * C, dbias);
+        count_launch((flags & 1) ? 3 : 4);
+    } else {
+        size_t n4 = rows * C / 4;
+        size_t g = (n4 + 255) / 256;
+        size_t cap = (size_t)num_sms() * 16;
+        attn_bwd_dq_finish_kernel<<<(unsigned)(g > cap ? cap : g), 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, rows, C);
+        count_launch((flags & 1) ? 2 : 3);
     }
+    rc = check_launch("attn_bwd_tc");
     return rc;
 }
