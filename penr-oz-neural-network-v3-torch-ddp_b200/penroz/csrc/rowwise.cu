@@ -512,28 +512,45 @@ layernorm_bwd_staged_kernel(const TG* __restrict__ dy, const float* __restrict__
     }
 }
 
-// out_q[c] += sum_blocks scratch[b][q][c]   (fixed summation order: deterministic). 32 columns x 32 partial-sum
-// lanes per CTA, so the several hundred per-block partials of a column are a few independent loads per thread.
+// out_q[c] += sum_blocks scratch[b][q][c]   (fixed summation order: deterministic). 32 columns (8 float4 lanes) x 128
+// partial-sum lanes per CTA, so the several hundred per-block partials of a column are four or five independent 16-byte
+// loads per thread -- the kernel is a chain of load latencies, not bandwidth.
 __global__ void __launch_bounds__(1024)
 layernorm_bwd_reduce_kernel(const float* __restrict__ scratch, int nblocks, int C, float* __restrict__ dgamma,
                             float* __restrict__ dbeta, float* __restrict__ dcol) {
-    __shared__ float sm[32][33];
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + tx;
+    __shared__ float4 sm[128][9];
+    const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+    const int c = blockIdx.x * 32 + tx * 4;
     const int qn = blockIdx.y;
     float* dst = (qn == 0) ? dgamma : (qn == 1) ? dbeta : dcol;
-    float s = 0.f;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (dst && c < C) {
 #pragma unroll 8
-        for (int b = ty; b < nblocks; b += 32) s += scratch[((size_t)b * 3 + qn) * C + c];
+        for (int b = ty; b < nblocks; b += 128) {
+            const float4 v = *reinterpret_cast<const float4*>(scratch + ((size_t)b * 3 + qn) * C + c);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
     }
     sm[ty][tx] = s;
     __syncthreads();
-    if (ty == 0 && dst && c < C) {
-        float t = sm[0][tx];
+    if (ty < 32) {
+        float4 t = sm[ty][tx];
 #pragma unroll
-        for (int k = 1; k < 32; ++k) t += sm[k][tx];
-        dst[c] += t;
+        for (int k = 1; k < 4; ++k) { const float4 v = sm[ty + 32 * k][tx]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+        sm[ty][tx] = t;
+    }
+    __syncthreads();
+    if (ty == 0 && dst && c < C) {
+        float4 t = sm[0][tx];
+#pragma unroll
+        for (int k = 1; k < 32; ++k) { const float4 v = sm[k][tx]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+        if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+            float4 o = *reinterpret_cast<float4*>(dst + c);
+            o.x += t.x; o.y += t.y; o.z += t.z; o.w += t.w;
+            *reinterpret_cast<float4*>(dst + c) = o;
+        } else {
+            dst[c] += t.x; dst[c + 1] += t.y; dst[c + 2] += t.z; dst[c + 3] += t.w;
+        }
     }
 }
 
