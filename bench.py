@@ -47,7 +47,7 @@ CONFIGS = {
                    name="GPT-2 124M KV-cache generation via generate_tokens, batch 1 and 64, 1024-token context"),
 }
 UNIT = "tokens/s"
-TRAFFIC_JSON = os.path.join(ROOT, "profiles", "r02n_ncu_launch_list_step.json")
+TRAFFIC_JSON = os.path.join(ROOT, "profiles", "r02p_ncu_launch_list_step.json")
 TRAFFIC_JSON_OLD = os.path.join(ROOT, "profiles", "r02_ncu_launch_list_step.json")
 
 
