@@ -78,8 +78,9 @@ int wstream_grid(int M, int N) {
         const int cap = max(1, num_sms() / ws_groups(M));
         return nunits < cap ? nunits : cap;
     }
-    // measured at batch 1 (124M head, 3142 units): 4 CTAs per SM's worth of shorter unit loops beat one resident CTA per
-    // SM looping 21 times (322 vs 369 us per token step), although the extra CTAs run as later waves
+    // one resident CTA per SM looping over its units, the next unit's weights in flight while the current one is reduced.
+    // Measured at 124M bf16 (the kernel holds 255 registers, so extra CTAs only run as later waves): token step at batch 1
+    // 347 us with 1 CTA per SM's worth of grid, 371 with 2, 375 with 4; batch 8: 494 / 518 / 522 (PENROZ_WS_PER_SM for A/B)
     static const int small_per_sm = getenv("PENROZ_WS_PER_SM") ? atoi(getenv("PENROZ_WS_PER_SM")) : 1;
     const int cap = num_sms() * small_per_sm;
     return nunits < cap ? nunits : cap;
