@@ -73,6 +73,7 @@ template <bool LAZY>
 __global__ void __launch_bounds__(320, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __restrict__ out,
                    float* __restrict__ lse, int Tn, int H, float scale_log2e) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
@@ -476,6 +477,7 @@ __global__ void attn_bwd_dq_finish_kernel(const float* __restrict__ acc, __nv_bf
 __global__ void __launch_bounds__(256)
 attn_bwd_finish_colsum_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int rows, int C,
                               float* __restrict__ part) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     __shared__ float sm[8][32][9];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int col = (blockIdx.x * 32 + tx) * 8;
@@ -538,6 +540,7 @@ attn_bwd_finish_colsum_kernel(const float* __restrict__ acc, __nv_bfloat16* __re
     }
 }
 __global__ void attn_bwd_bias_reduce_kernel(const float* __restrict__ part, int nparts, int N, float* __restrict__ out) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= N) return;
     float t = 0.f;
@@ -567,6 +570,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                    const __grid_constant__ CUtensorMap tmDQ,
                    const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_accum,
                    __nv_bfloat16* __restrict__ dqkv, int Tn, int H, float scale, float scale_log2e) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;

@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(512)
 ce_rows_bf16_kernel(__nv_bfloat16* __restrict__ logits, long long ld, const long long* __restrict__ tgt, int V,
                     long long ignore_index, const int* __restrict__ n_valid, float grad_scale,
                     float* __restrict__ loss_rows, int* __restrict__ err_flag) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     __shared__ float red[32];
     constexpr float kLog2e = 1.44269504088896340736f;
     const int row = blockIdx.x;

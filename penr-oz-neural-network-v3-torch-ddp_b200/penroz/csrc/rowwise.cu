@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(256)
 layernorm_fwd_reg_kernel(const TX* __restrict__ x, const TW* __restrict__ gamma, const TW* __restrict__ beta,
                          TO* __restrict__ out, float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
                          int C, float eps) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= rows) return;
     const int lane = threadIdx.x & 31;
@@ -377,6 +378,7 @@ layernorm_bwd_staged_kernel(const TG* __restrict__ dy, const float* __restrict__
                             const float* __restrict__ mean, const float* __restrict__ rstd,
                             const float* __restrict__ add, float* __restrict__ dx, __nv_bfloat16* __restrict__ dx_bf16,
                             float* __restrict__ scratch, int rows, int C, int S, int want_dcol) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     extern __shared__ __align__(128) unsigned char ln_smem[];
     __shared__ __align__(16) float red[2][R][2][8];
     __shared__ __align__(8) unsigned long long full_bar[8];
@@ -518,6 +520,7 @@ layernorm_bwd_staged_kernel(const TG* __restrict__ dy, const float* __restrict__
 __global__ void __launch_bounds__(1024)
 layernorm_bwd_reduce_kernel(const float* __restrict__ scratch, int nblocks, int C, float* __restrict__ dgamma,
                             float* __restrict__ dbeta, float* __restrict__ dcol) {
+    pdl_trigger();   // a dependent-launch successor (the next GEMM) may set itself up while this grid drains
     __shared__ float4 sm[128][9];
     const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
     const int c = blockIdx.x * 32 + tx * 4;
